@@ -1,0 +1,278 @@
+// oracle/rt_scenes.hpp — restatement of /root/reference/src/Scenes.hs (scene constructors + cameras) and of the
+// config-5 synthetic scene described in BASELINE.md, on top of rt_oracle.hpp.  TEST INFRASTRUCTURE ONLY.
+// RNG draw order follows the monadic order of the Haskell source line by line.
+#pragma once
+#include "rt_oracle.hpp"
+
+namespace orc {
+
+// lightsMode: 0 = literal HEAD light list; 1 = "lit" variant (a usable light list so that the HEAD mixture pdf
+// never degenerates to 0/0) — used for NaN-free radiance parity, never for the literal configs.
+struct SceneArgs { double t0 = 0.0, t1 = 1.0; std::shared_ptr<ImageData> earth; int earthW = 0, earthH = 0; int lightsMode = 0; int synthN = 1000; };
+
+inline HitP phantomLight() {  // not in the world; only a sampling target for lit variants of sky-lit scenes
+  return sphere(V3d(0, 60, 0), 10, diffuseLight(constantColor(1, 1, 1)));
+}
+
+// Scenes.hs:32-73
+inline Scene makeCornellBoxScene(const SceneArgs& a, SMGen gen) {
+  MatP red = lambertian(constantColor(0.65, 0.05, 0.05));
+  MatP white = lambertian(constantColor(0.73, 0.73, 0.73));
+  MatP green = lambertian(constantColor(0.12, 0.45, 0.15));
+  MatP light = diffuseLight(constantColor(15, 15, 15));
+  HitP lightHittable = rect(XZPlane, 213, 343, 227, 332, 554, light);
+  HitP box1 = translate(V3d(265, 0, 295), rotate(YAxis, 15, cuboid(V3d(0, 0, 0), V3d(165, 330, 165), white)));
+  HitP glassSphere = sphere(V3d(190, 90, 190), 90, dielectric(1.5));
+  Scene s;
+  s.world = makeBVH(gen, {rect(YZPlane, 0, 555, 0, 555, 555, green), rect(YZPlane, 0, 555, 0, 555, 0, red), lightHittable,
+                          rect(XZPlane, 0, 555, 0, 555, 0, white), rect(XZPlane, 0, 555, 0, 555, 555, white),
+                          rect(XYPlane, 0, 555, 0, 555, 555, white), box1, glassSphere});
+  s.lights = makeBVH(gen, {lightHittable, glassSphere});
+  s.g1 = gen;
+  (void)a;
+  return s;
+}
+
+// Scenes.hs:75-118
+inline Scene makeCornellSmokeBoxScene(const SceneArgs& a, SMGen gen) {
+  MatP light = diffuseLight(constantColor(7, 7, 7));
+  HitP lightHittable = rect(XZPlane, 113, 443, 127, 432, 554, light);
+  MatP red = lambertian(constantColor(0.65, 0.05, 0.05));
+  MatP white = lambertian(constantColor(0.73, 0.73, 0.73));
+  MatP green = lambertian(constantColor(0.12, 0.45, 0.15));
+  Scene s;
+  s.world = makeBVH(gen, {rect(YZPlane, 0, 555, 0, 555, 555, green), rect(YZPlane, 0, 555, 0, 555, 0, red), lightHittable,
+                          rect(XZPlane, 0, 555, 0, 555, 0, white), rect(XZPlane, 0, 555, 0, 555, 555, white),
+                          rect(XYPlane, 0, 555, 0, 555, 555, white),
+                          constantMedium(0.01, constantColor(0, 0, 0),
+                                         translate(V3d(265, 0, 295), rotate(YAxis, 15, cuboid(V3d(0, 0, 0), V3d(165, 330, 165), white)))),
+                          constantMedium(0.01, constantColor(1, 1, 1),
+                                         translate(V3d(130, 0, 65), rotate(YAxis, -18, cuboid(V3d(0, 0, 0), V3d(165, 165, 165), white))))});
+  s.lights = lightHittable;
+  s.g1 = gen;
+  (void)a;
+  return s;
+}
+
+// Scenes.hs:120-131
+inline Camera cornellCamera(int W, int H) {
+  return newCamera(V3d(278, 278, -800), V3d(278, 278, 0.0), V3d(0, 1, 0), 40.0, (double)W / (double)H, 0.0, 10.0, 0.0, 1.0);
+}
+
+// Scenes.hs:133-155
+inline Scene makeSimpleLightScene(const SceneArgs& a, SMGen gen) {
+  MatP difflight = diffuseLight(constantColor(4, 4, 4));
+  HitP sphereLight = sphere(V3d(0, 7, 0), 2, difflight);
+  HitP rectLight = rect(XYPlane, 3, 5, 1, 3, -2, difflight);
+  TexP perText = makePerlin(gen, 1.0);
+  Scene s;
+  s.world = makeBVH(gen, {sphere(V3d(0, -1000, 0), 1000, lambertian(perText)), sphere(V3d(0, 2, 0), 2, lambertian(perText)), sphereLight, rectLight});
+  s.lights = makeBVH(gen, {sphereLight, rectLight});
+  if (a.lightsMode == 1) s.lights = sphereLight;
+  s.g1 = gen;
+  return s;
+}
+
+// Scenes.hs:167-179
+inline Scene makeEarthScene(const SceneArgs& a, SMGen gen) {
+  TexP earthTex = imageTexture(a.earth, a.earthW, a.earthH);
+  Scene s;
+  s.world = makeBVH(gen, {sphere(V3d(0, 0, 0), 2, lambertian(earthTex))});
+  s.lights = a.lightsMode == 1 ? phantomLight() : unhittable();
+  s.background[0] = s.background[1] = s.background[2] = 1.0;
+  s.g1 = gen;
+  return s;
+}
+
+// Scenes.hs:181-192
+inline Camera twoSpheresSceneCamera(int W, int H) {
+  return newCamera(V3d(26, 4, 6), V3d(0, 2, 0), V3d(0, 1, 0), 20.0, (double)W / (double)H, 0.1, 20.0, 0.0, 1.0);
+}
+
+// Scenes.hs:194-211
+inline Scene makeTwoPerlinSpheresScene(const SceneArgs& a, SMGen gen) {
+  TexP perText = makePerlin(gen, 1.5);
+  Scene s;
+  s.world = makeBVH(gen, {sphere(V3d(0, -1000, 0), 1000, lambertian(perText)), sphere(V3d(0, 2, 0), 2, lambertian(perText))});
+  s.lights = a.lightsMode == 1 ? phantomLight() : unhittable();
+  s.g1 = gen;
+  return s;
+}
+
+// Scenes.hs:213-237
+inline Scene makeTwoSpheresScene(const SceneArgs& a, SMGen gen) {
+  MatP checkerMaterial = metal(checkerTexture(constantColor(0.2, 0.3, 0.1), constantColor(0.9, 0.9, 0.9)), 0.0);
+  MatP flatMaterial = lambertian(constantColor(0.6, 0.2, 0.1));
+  Scene s;
+  s.world = makeBVH(gen, {sphere(V3d(0, -10, 0), 10, checkerMaterial), sphere(V3d(0, 10, 0), 10, flatMaterial)});
+  s.lights = a.lightsMode == 1 ? phantomLight() : unhittable();
+  s.background[0] = 0.8; s.background[1] = 0.8; s.background[2] = 0.9;
+  s.g1 = gen;
+  return s;
+}
+
+// Scenes.hs:239-250
+inline Camera randomSceneCamera(int W, int H) {
+  return newCamera(V3d(13, 2, 3), V3d(0, 0, 0), V3d(0, 1, 0), 20.0, (double)W / (double)H, 0.1, 10.0, 0.0, 1.0);
+}
+
+// Scenes.hs:253-317 (moving=false) and 321-399 (moving=true; the "tweaked" Next Week variant)
+inline Scene makeRandomSceneImpl(const SceneArgs& a, SMGen gen, bool nextWeek) {
+  HitP ground, s1, s2;
+  if (!nextWeek) {
+    ground = sphere(V3d(0, -1000, 0), 1000, lambertian(constantColor(0.5, 0.5, 0.5)));
+    s1 = sphere(V3d(0, 1, 0), 1.0, dielectric(1.5));
+    s2 = sphere(V3d(-4, 1, 0), 1.0, lambertian(constantColor(0.4, 0.2, 0.1)));
+  } else {
+    ground = sphere(V3d(0, -1000, 0), 1000, lambertian(checkerTexture(constantColor(0.2, 0.3, 0.1), constantColor(0.9, 0.9, 0.9))));
+    s1 = cuboid(V3d(-0.75, 0.0, -0.75), V3d(0.75, 1.5, 0.75), dielectric(1.5));
+    s2 = sphere(V3d(-4, 1, 0), 1.0, lambertian(imageTexture(a.earth, a.earthW, a.earthH)));
+  }
+  HitP s3 = sphere(V3d(4, 1, 0), 1.0, metal(constantColor(0.7, 0.6, 0.5), 0.0));
+  std::vector<HitP> objs = {ground, s1, s2, s3};
+  for (int aa = -11; aa <= 10; ++aa) for (int bb = -11; bb <= 10; ++bb) {  // makeRandomSphereM
+    double mat = randomDoubleM(gen);
+    double px = randomDoubleM(gen);
+    double py = randomDoubleM(gen);
+    V3d center((double)aa + 0.9 * px, 0.2, (double)bb + 0.9 * py);
+    if (length(center - V3d(4.0, 0.2, 0)) <= 0.9) continue;
+    if (mat < 0.8) {
+      V3d a1 = randomVec3DoubleM(gen);
+      V3d a2 = randomVec3DoubleM(gen);
+      if (nextWeek) {
+        double mx = randomDoubleRM(gen, -0.25, 0.25);
+        double mz = randomDoubleRM(gen, -0.25, 0.25);
+        V3d alb = a1 * a2;
+        objs.push_back(movingSphere(center, center + V3d(mx, 0, mz), 0.0, 1.0, 0.2, lambertian(constantColor(alb.x, alb.y, alb.z))));
+      } else {
+        V3d alb = a1 * a2;
+        objs.push_back(sphere(center, 0.2, lambertian(constantColor(alb.x, alb.y, alb.z))));
+      }
+    } else if (mat < 0.95) {
+      V3d alb = randomVec3DoubleRM(gen, 0.5, 1.0);
+      double fuzz = randomDoubleRM(gen, 0.0, 0.5);
+      objs.push_back(sphere(center, 0.2, metal(constantColor(alb.x, alb.y, alb.z), fuzz)));
+    } else {
+      objs.push_back(sphere(center, 0.2, dielectric(1.5)));
+    }
+  }
+  Scene s;
+  s.world = makeBVH(gen, objs);
+  s.lights = a.lightsMode == 1 ? phantomLight() : unhittable();
+  s.background[0] = 0.7; s.background[1] = 0.8; s.background[2] = 0.9;
+  s.g1 = gen;
+  return s;
+}
+inline Scene makeRandomSceneBookOne(const SceneArgs& a, SMGen gen) { return makeRandomSceneImpl(a, gen, false); }
+inline Scene makeRandomScene(const SceneArgs& a, SMGen gen) { return makeRandomSceneImpl(a, gen, true); }
+
+// Scenes.hs:401-412
+inline Camera nextWeekFinalSceneCamera(int W, int H) {
+  return newCamera(V3d(575, 278, -525), V3d(320, 278, 0.0), V3d(0, 1, 0), 40.0, (double)W / (double)H, 0.1, 580.0, 0.0, 1.0);
+}
+
+// Scenes.hs:414-466
+inline Scene makeNextWeekFinalScene(const SceneArgs& a, SMGen gen) {
+  MatP ground = lambertian(constantColor(0.48, 0.83, 0.53));
+  MatP white = lambertian(constantColor(0.73, 0.73, 0.73));
+  const double w = 100, y0 = 0;
+  std::vector<HitP> b1;
+  for (int ii = 0; ii <= 19; ++ii) for (int jj = 0; jj <= 19; ++jj) {
+    double i = ii, j = jj;
+    double x0 = i * w - 1000, z0 = j * w - 1000;
+    double x1 = x0 + w;
+    double y1 = randomDoubleRM(gen, 1, 101);
+    double z1 = z0 + w;
+    b1.push_back(cuboid(V3d(x0, y0, z0), V3d(x1, y1, z1), ground));
+  }
+  HitP boxes1 = makeBVH(gen, b1);
+  MatP light = diffuseLight(constantColor(7, 7, 7));
+  HitP boundary1 = sphere(V3d(360, 150, 145), 70, dielectric(1.5));
+  HitP boundary2 = sphere(V3d(0, 0, 0), 5000, dielectric(1.5));
+  TexP pertext = makePerlin(gen, 0.1);
+  std::vector<HitP> b2;
+  for (int i = 0; i < 1000; ++i) { V3d p = randomVec3DoubleRM(gen, 0, 165); b2.push_back(sphere(p, 10, white)); }
+  HitP boxes2 = makeBVH(gen, b2);
+  HitP lightRect = rect(XZPlane, 113, 443, 127, 432, 554, light);
+  Scene s;
+  s.world = makeBVH(gen, {boxes1, lightRect,
+                          movingSphere(V3d(400, 400, 200), V3d(430, 400, 200), a.t0, a.t1, 50, lambertian(constantColor(0.7, 0.3, 0.1))),
+                          sphere(V3d(260, 150, 45), 50, dielectric(1.5)),
+                          sphere(V3d(0, 150, 145), 50, metal(constantColor(0.8, 0.8, 0.9), 10.0)),
+                          boundary1,
+                          constantMedium(0.2, constantColor(0.2, 0.4, 0.9), boundary1),
+                          constantMedium(0.0001, constantColor(1, 1, 1), boundary2),
+                          sphere(V3d(400, 200, 400), 100, lambertian(imageTexture(a.earth, a.earthW, a.earthH))),
+                          sphere(V3d(220, 280, 300), 80, lambertian(pertext)),
+                          translate(V3d(-100, 270, 395), rotate(YAxis, 15, boxes2))});
+  s.lights = a.lightsMode == 1 ? lightRect : unhittable();
+  s.g1 = gen;
+  return s;
+}
+
+// Config 5 (not in the reference, built with the reference's constructors):
+// n x n spheres r=0.2 on a jittered grid, Book-1 material mix in makeRandomSphereM's draw order, XZ-rect ground,
+// one overhead XZ-rect light which is also the light list, makeBVH over everything.
+inline Scene makeSyntheticScene(const SceneArgs& a, SMGen gen) {
+  int n = a.synthN; int lo = -(n / 2);
+  double ext = (double)n / 2 + 1;
+  std::vector<HitP> objs;
+  objs.reserve((size_t)n * n + 2);
+  objs.push_back(rect(XZPlane, -ext, ext, -ext, ext, 0.0, lambertian(constantColor(0.5, 0.5, 0.5))));
+  HitP lightRect = rect(XZPlane, -ext * 0.5, ext * 0.5, -ext * 0.5, ext * 0.5, ext, diffuseLight(constantColor(4, 4, 4)));
+  objs.push_back(lightRect);
+  for (int aa = lo; aa < lo + n; ++aa) for (int bb = lo; bb < lo + n; ++bb) {
+    double mat = randomDoubleM(gen);
+    double px = randomDoubleM(gen);
+    double py = randomDoubleM(gen);
+    V3d center((double)aa + 0.9 * px, 0.2, (double)bb + 0.9 * py);
+    if (mat < 0.8) {
+      V3d a1 = randomVec3DoubleM(gen); V3d a2 = randomVec3DoubleM(gen); V3d alb = a1 * a2;
+      objs.push_back(sphere(center, 0.2, lambertian(constantColor(alb.x, alb.y, alb.z))));
+    } else if (mat < 0.95) {
+      V3d alb = randomVec3DoubleRM(gen, 0.5, 1.0); double fuzz = randomDoubleRM(gen, 0.0, 0.5);
+      objs.push_back(sphere(center, 0.2, metal(constantColor(alb.x, alb.y, alb.z), fuzz)));
+    } else {
+      objs.push_back(sphere(center, 0.2, dielectric(1.5)));
+    }
+  }
+  Scene s;
+  s.world = makeBVH(gen, std::move(objs));
+  s.lights = lightRect;
+  s.background[0] = 0.7; s.background[1] = 0.8; s.background[2] = 0.9;
+  s.g1 = gen;
+  return s;
+}
+// elevated look-down camera for config 5, aperture 0; scaled with the grid so the whole field is in view
+inline Camera syntheticCamera(int W, int H, int n) {
+  double e = (double)n / 2;
+  return newCamera(V3d(0.9 * e, 0.45 * e, 0.9 * e), V3d(0, 0, 0), V3d(0, 1, 0), 40.0, (double)W / (double)H, 0.0, 10.0, 0.0, 1.0);
+}
+
+inline Scene makeSceneByName(const std::string& name, const SceneArgs& a, int64_t seed) {
+  SMGen gen = randGen(seed);
+  Scene s;
+  if (name == "cornell") s = makeCornellBoxScene(a, gen);
+  else if (name == "cornell_smoke") s = makeCornellSmokeBoxScene(a, gen);
+  else if (name == "simple_light") s = makeSimpleLightScene(a, gen);
+  else if (name == "earth") s = makeEarthScene(a, gen);
+  else if (name == "two_perlin") s = makeTwoPerlinSpheresScene(a, gen);
+  else if (name == "two_spheres") s = makeTwoSpheresScene(a, gen);
+  else if (name == "random_book1") s = makeRandomSceneBookOne(a, gen);
+  else if (name == "random") s = makeRandomScene(a, gen);
+  else if (name == "next_week_final") s = makeNextWeekFinalScene(a, gen);
+  else if (name == "synthetic") s = makeSyntheticScene(a, gen);
+  else throw std::runtime_error("unknown scene: " + name);
+  s.number();
+  return s;
+}
+inline Camera cameraByName(const std::string& name, int W, int H, int synthN) {
+  if (name == "cornell" || name == "cornell_smoke") return cornellCamera(W, H);
+  if (name == "simple_light" || name == "earth" || name == "two_perlin" || name == "two_spheres") return twoSpheresSceneCamera(W, H);
+  if (name == "random_book1" || name == "random") return randomSceneCamera(W, H);
+  if (name == "next_week_final") return nextWeekFinalSceneCamera(W, H);
+  if (name == "synthetic") return syntheticCamera(W, H, synthN);
+  throw std::runtime_error("unknown camera: " + name);
+}
+
+}  // namespace orc

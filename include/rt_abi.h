@@ -1,0 +1,235 @@
+/* rt_abi.h — C ABI of librt_b200.so: the B200 path-tracing core behind the reference's render entry point.
+ *
+ * What it replaces (paths relative to the reference checkout):
+ *   runRender :: RenderStaticEnv -> [RandGen] -> [Vector RGB]        src/Lib.hs:1491-1523
+ *   and everything runRender reaches per sample: uniformRandomUVs (1352-1371), renderPos/sampleColor (1335-1350),
+ *   getRay (1253-1267), rayColor (1298-1333), hit (970-1109), boxRayIntersect (798-814), scatter/scatteringPdf/
+ *   emitted (819-903), pdfGenerate/pdfValue (362-382), htblPdfValue/htblRandom (662-724), textureValue/noise/turb
+ *   (441-513), the samplers (1119-1228).
+ * The reference has no FFI today (package.yaml:25-35 has no c-sources / extra-libraries); INTEGRATION.md shows the
+ * `foreign import ccall` stubs and the flattener a maintainer adds inside Lib.  Scene construction (Scenes.hs, the
+ * Lib smart constructors, makeBVH, makePerlin, newCamera) stays on the host and arrives here as the flat
+ * struct-of-arrays RtSceneDesc below.  All reals cross the boundary as the host's Double; the library rounds
+ * them to fp32 (round-to-nearest-even) when it uploads for the fp32 kernels.
+ *
+ * Conventions: every function returns 0 on success and a negative RT_ERR_* code on failure; rt_last_error()
+ * returns a thread-local message.  Host pointers are borrowed for the duration of the call only.  The library
+ * never falls back to a CPU implementation: without a usable CUDA device every compute entry point fails with
+ * RT_ERR_CUDA.
+ */
+#ifndef RT_ABI_H
+#define RT_ABI_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_ABI_VERSION 1
+
+/* error codes */
+#define RT_OK 0
+#define RT_ERR_ARG (-1)        /* null pointer, bad size, bad enum, index out of range in the scene description */
+#define RT_ERR_UNSUPPORTED (-2) /* nesting deeper than the compiled traversal budget (see rt_limits) */
+#define RT_ERR_CUDA (-3)       /* no device, allocation failure, launch failure (message has the CUDA error string) */
+#define RT_ERR_HANDLE (-4)     /* unknown / destroyed scene handle */
+
+/* Hittable reference = (kind << 28) | index-within-kind.  Kinds follow the constructors of
+ * `data Hittable` (Lib.hs:521-585) with `Rect` split by its Rectangle constructor (Lib.hs:607-647); the three rect
+ * kinds index one shared rect array. */
+enum RtHittableKind {
+  RT_UNHITTABLE = 0,
+  RT_SPHERE = 1,
+  RT_MOVING_SPHERE = 2,
+  RT_RECT_XY = 3,
+  RT_RECT_XZ = 4,
+  RT_RECT_YZ = 5,
+  RT_CUBOID = 6,
+  RT_BVH_NODE = 7,
+  RT_TRANSLATE = 8,
+  RT_ROTATE = 9,
+  RT_CONSTANT_MEDIUM = 10
+};
+#define RT_REF(kind, index) ((((uint32_t)(kind)) << 28) | ((uint32_t)(index) & 0x0fffffffu))
+#define RT_REF_KIND(ref) ((ref) >> 28)
+#define RT_REF_INDEX(ref) ((ref) & 0x0fffffffu)
+#define RT_NONE 0xffffffffu
+
+/* `data Material` (Lib.hs:339-345) and `data Texture` (Lib.hs:394-419) */
+enum RtMaterialKind { RT_LAMBERTIAN = 0, RT_METAL = 1, RT_DIELECTRIC = 2, RT_DIFFUSE_LIGHT = 3, RT_ISOTROPIC = 4 };
+enum RtTextureKind { RT_TEX_CONSTANT = 0, RT_TEX_CHECKER = 1, RT_TEX_PERLIN = 2, RT_TEX_IMAGE = 3 };
+enum RtAxis { RT_AXIS_X = 0, RT_AXIS_Y = 1, RT_AXIS_Z = 2 }; /* data Axis, Lib.hs:515 */
+
+/* Flattened scene: `type Scene = (Hittable, Hittable, Albedo)` (Lib.hs:84) + `data Camera` (Lib.hs:1230-1251).
+ * Arrays may be NULL when their count is 0. */
+typedef struct RtSceneDesc {
+  uint32_t abi_version; /* RT_ABI_VERSION */
+
+  /* BVHNode left right box size (Lib.hs:552-560) */
+  uint32_t n_nodes;
+  const double* node_box;     /* [n][6] min.xyz max.xyz */
+  const uint32_t* node_left;  /* [n] ref */
+  const uint32_t* node_right; /* [n] ref */
+  const uint32_t* node_size;  /* [n] bvh_size (number of objects below; used by htblRandom / htblPdfValue weights) */
+
+  /* Sphere center radius material (Lib.hs:522-528) */
+  uint32_t n_spheres;
+  const double* sphere_cr;    /* [n][4] cx cy cz r */
+  const uint32_t* sphere_mat; /* [n] material index */
+
+  /* MovingSphere c0 c1 t0 t1 duration r material (Lib.hs:529-543); t1 is not used by `hit` */
+  uint32_t n_moving;
+  const double* moving;       /* [n][9] c0.xyz c1.xyz t0 duration r */
+  const uint32_t* moving_mat; /* [n] */
+
+  /* Rect (XYRect|XZRect|YZRect) a0 a1 b0 b1 k material (Lib.hs:607-647); the plane is the ref's kind */
+  uint32_t n_rects;
+  const double* rect;         /* [n][5] a0 a1 b0 b1 k */
+  const uint32_t* rect_mat;   /* [n] */
+
+  /* Cuboid min max [six Rects] (Lib.hs:545-551); the rect list is always the one `cuboid` builds (Lib.hs:594-605) */
+  uint32_t n_cuboids;
+  const double* cuboid;       /* [n][6] min.xyz max.xyz */
+  const uint32_t* cuboid_mat; /* [n] */
+
+  /* Translate offset child (Lib.hs:561-565) */
+  uint32_t n_translates;
+  const double* translate_off;     /* [n][3] */
+  const uint32_t* translate_child; /* [n] ref */
+
+  /* Rotate axis sinTheta cosTheta box child (Lib.hs:566-576); the box is only used by the parent BVH */
+  uint32_t n_rotates;
+  const double* rotate_sc;       /* [n][2] sin cos */
+  const uint32_t* rotate_axis;   /* [n] RtAxis */
+  const uint32_t* rotate_child;  /* [n] ref */
+
+  /* ConstantMedium negInvDensity material boundary (Lib.hs:577-583) */
+  uint32_t n_media;
+  const double* medium_neg_inv_density; /* [n] */
+  const uint32_t* medium_mat;           /* [n] material index (Isotropic) */
+  const uint32_t* medium_boundary;      /* [n] ref */
+
+  uint32_t n_materials;
+  const uint32_t* mat_kind;  /* [n] RtMaterialKind */
+  const uint32_t* mat_tex;   /* [n] texture index or RT_NONE (Dielectric) */
+  const double* mat_param;   /* [n] Fuzz / RefractiveIdx, else 0 */
+
+  uint32_t n_textures;
+  const uint32_t* tex_kind;  /* [n] RtTextureKind */
+  const double* tex_rgb;     /* [n][3] ConstantColor albedo */
+  const uint32_t* tex_a;     /* [n] checker: odd texture; perlin: table index; image: image index or RT_NONE (= ImageTexture Nothing) */
+  const uint32_t* tex_b;     /* [n] checker: even texture */
+  const double* tex_scale;   /* [n] perlinScale */
+
+  /* Perlin ranvec permX permY permZ (Lib.hs:401-410) */
+  uint32_t n_perlin;
+  const double* perlin_ranvec; /* [n][256][3] */
+  const int32_t* perlin_perm;  /* [n][3][256] X, Y, Z */
+
+  /* ImageTexture pixels (JP.Image PixelRGB8, Lib.hs:384-389), tightly packed RGB8 rows, top row first */
+  uint32_t n_images;
+  const uint8_t* const* image_rgb; /* [n] -> [h][w][3] */
+  const uint32_t* image_w;
+  const uint32_t* image_h;
+
+  uint32_t world_root;  /* ref: fst of Scene */
+  uint32_t lights_root; /* ref: snd of Scene (RT_REF(RT_UNHITTABLE,0) for `Unhittable`) */
+  double background[3]; /* thd of Scene */
+  double camera[24];    /* origin llc horiz vert u v w (7 x xyz), lensRadius, t0, t1 (Lib.hs:1230-1251) */
+} RtSceneDesc;
+
+/* arithmetic of the device path */
+enum RtPrecision {
+  RT_PREC_F32 = 0,   /* fp32 everywhere (the production path) */
+  RT_PREC_MIXED = 1, /* fp32, sphere quadratic (Lib.hs:1091-1095) in fp64 */
+  RT_PREC_F64 = 2    /* fp64 everywhere: the reference's Double arithmetic, for validation */
+};
+#define RT_FLAG_FAST_MATH 1u /* allow FMA contraction, reciprocal slab test and fast transcendentals (not bit-exact vs the fp32 oracle) */
+
+typedef struct RtRenderParams {
+  uint32_t width, height;     /* full image size (imageWidth, imageHeight of mkRenderStaticEnv, Lib.hs:92-108) */
+  uint32_t sample_offset;     /* first sample index rendered by this call */
+  uint32_t sample_count;      /* samples per pixel rendered by this call (numSamples when offset = 0) */
+  uint32_t total_samples;     /* informational: the frame's numSamples (the caller divides the sums by it) */
+  uint32_t max_depth;         /* maxDepth */
+  uint32_t row0, row1;        /* rows [row0,row1) rendered by this call (row 0 = top of the image); 0,0 = all */
+  uint32_t col0, col1;        /* columns [col0,col1); 0,0 = all */
+  uint64_t seed;              /* stream seed: sample s of pixel p uses streamGen(seed, p, s) (DESIGN.md "RNG") */
+  uint32_t precision;         /* RtPrecision */
+  uint32_t flags;             /* RT_FLAG_* */
+  int32_t device;             /* CUDA device ordinal, -1 = current */
+  uint32_t reserved;
+} RtRenderParams;
+
+typedef struct RtStats {
+  double kernel_ms;        /* device time of the render kernel(s), CUDA events on the launching stream */
+  double h2d_ms, d2h_ms;   /* copies inside this call (0 for the *_device entry points) */
+  uint64_t samples;        /* camera paths traced by this call */
+  uint64_t launches;       /* kernels launched by this call */
+  uint64_t counters[16];   /* RT_CTR_* when the call was made with counters enabled, else 0 */
+} RtStats;
+/* counters (algorithmic work, same definitions as the oracle's): */
+enum RtCounter { RT_CTR_PATHS = 0, RT_CTR_BOUNCES = 1, RT_CTR_BOX_TESTS = 2, RT_CTR_SPHERE_TESTS = 3, RT_CTR_MOVING_TESTS = 4,
+                 RT_CTR_RECT_TESTS = 5, RT_CTR_CUBOID_TESTS = 6, RT_CTR_TRANSLATE = 7, RT_CTR_ROTATE = 8, RT_CTR_MEDIUM = 9,
+                 RT_CTR_SPHERE_HITS = 10, RT_CTR_NOISE_CALLS = 11, RT_CTR_TEXELS = 12, RT_CTR_QUERIES = 13, RT_CTR_VISITS = 14,
+                 RT_CTR_UNHITTABLE = 15 };
+
+typedef struct RtLimits {
+  uint32_t max_stack;        /* traversal stack entries per path the kernels can be launched with */
+  uint32_t max_frames;       /* nested Translate/Rotate frames above one primitive */
+  uint32_t max_medium_depth; /* ConstantMedium inside a ConstantMedium boundary */
+  uint32_t max_light_depth;  /* depth of the lights BVH walked by htblPdfValue */
+} RtLimits;
+
+typedef uint64_t rt_scene_t;
+
+int rt_abi_version(void);
+const char* rt_last_error(void);
+int rt_device_count(void);             /* number of usable CUDA devices (0 if none) */
+int rt_get_limits(RtLimits* out);
+
+/* Validates and uploads a scene to `device` (-1 = current).  Replaces nothing in the reference: it is the
+ * receiving end of the flattener. */
+int rt_scene_create(const RtSceneDesc* desc, int device, rt_scene_t* out);
+int rt_scene_destroy(rt_scene_t scene);
+
+/* runRender's numeric core (Lib.hs:1491-1523 minus albedoToColor): adds, for every pixel of the requested region,
+ * the radiance of samples [sample_offset, sample_offset+sample_count) to out_rgb_sum.
+ *   out_rgb_sum: HOST double[height*width*3], row 0 = top row (y = height-1, Lib.hs:1488-1489); the call
+ *   OVERWRITES the region it renders with that call's sums (other pixels are left untouched).
+ * The caller divides by numSamples (Lib.hs:1349) and applies albedoToColor (Lib.hs:287-292) — or calls rt_tonemap. */
+int rt_render(rt_scene_t scene, const RtRenderParams* params, double* out_rgb_sum, RtStats* stats);
+
+/* Same, with out_rgb_sum a DEVICE pointer on the scene's device (double[height*width*3]); the kernel ACCUMULATES
+ * into it (the caller zeroes it), on `cuda_stream` (a cudaStream_t passed as void*, NULL = default stream), and
+ * the call returns without synchronising unless stats != NULL.  Used by the multi-GPU host to reduce partial
+ * framebuffers with NCCL without host staging. */
+int rt_render_device(rt_scene_t scene, const RtRenderParams* params, double* d_out_rgb_sum, void* cuda_stream, RtStats* stats);
+
+/* Same as rt_render with the algorithmic-work counters of RtStats filled (slower instrumented kernel). */
+int rt_render_counted(rt_scene_t scene, const RtRenderParams* params, double* out_rgb_sum, RtStats* stats);
+
+/* `hit world ray t_min t_max` (Lib.hs:970-1109) for n explicit rays — the parity probe for hit ids and BVH
+ * traversal order.  rays: [n][7] origin dir time.  Media draw from streamGen(seed, ray index, 0).
+ * Outputs (host arrays, any may be NULL): hit[n] 0/1; rec[n][9] = t p.xyz normal.xyz u v; prim[n] ref of the
+ * primitive (sphere / rect / cuboid / medium) that produced the hit; mat[n] material index; front[n] frontFace;
+ * nvisit[n] number of `hit` invocations; vhash[n] FNV-1a-style hash of the visited refs in order;
+ * vlog[n][log_stride] first log_stride visited refs (RT_NONE padded). */
+int rt_trace(rt_scene_t scene, uint32_t precision, uint32_t flags, uint32_t n, const double* rays, double t_min, double t_max,
+             uint64_t seed, uint32_t log_stride, int32_t* hit, double* rec, uint32_t* prim, uint32_t* mat, uint8_t* front,
+             uint64_t* nvisit, uint64_t* vhash, uint32_t* vlog);
+
+/* textureValue (Lib.hs:496-513) probe: q[n][5] = u v p.xyz -> out[n][3] */
+int rt_texture_value(rt_scene_t scene, uint32_t tex, uint32_t precision, uint32_t n, const double* q, double* out);
+
+/* albedoToColor (Lib.hs:287-292) on the device: mean = sum / total_samples, sqrt, clamp [0,0.999], *256, floor.
+ * in: host double[n] sums; out: host uint8[n].  NaN maps to 0 (GHC's floor NaN :: Word8 is platform-defined). */
+int rt_tonemap(const double* rgb_sum, uint32_t n, uint32_t total_samples, uint8_t* out_rgb8);
+
+void rt_shutdown(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_ABI_H */

@@ -1,0 +1,261 @@
+"""GPU parity tests (run on the B200 box): every check goes through the C ABI of librt_b200.so and compares with the CPU oracle
+on the same seeded inputs.
+
+Bars (north_star):
+  * hit ids, hit t and BVH traversal order: BIT-EXACT — fp64 kernels vs oracle<double> (= the reference's arithmetic) and
+    fp32 kernels vs oracle<float>, on a fixed ray set (pixel-centre primary rays + seeded random rays);
+  * radiance: per-(pixel,sample) streams are shared with the oracle, so images are compared pixel-for-pixel.  Tolerance:
+    at least 90 % of pixels within 1e-3 relative (paths only separate where libm/CUDA transcendentals differ in the last
+    ulp and flip a comparison) and the image mean within 2 %; fp32 vs the reference's Double additionally by converged-mean
+    RMSE against the oracle's own seed-to-seed noise floor.
+"""
+import numpy as np
+import pytest
+
+from conftest import EARTH_SCENES
+
+pytestmark = pytest.mark.gpu
+
+ALL = ["cornell", "cornell_smoke", "simple_light", "earth", "two_perlin", "two_spheres", "random_book1", "random", "next_week_final", "synthetic"]
+NO_MEDIA = [s for s in ALL if s not in ("cornell_smoke", "next_week_final")]
+W, H = 60, 40
+
+
+def _rays(O, osc, seed=5, n_rand=3000):
+    cam = osc.camera(W, H)
+    prim = O.primary_rays(cam, W, H, time=0.25)
+    rng = np.random.default_rng(seed)
+    # random rays from around the camera origin in random directions, random shutter times
+    o = cam[0:3] + rng.normal(size=(n_rand, 3)) * (np.linalg.norm(cam[0:3]) * 0.2 + 1.0)
+    d = rng.normal(size=(n_rand, 3))
+    t = rng.random((n_rand, 1))
+    return np.concatenate([prim, np.concatenate([o, d, t], 1)], 0)
+
+
+@pytest.fixture(scope="module")
+def dev_scene(gpu):
+    cache = {}
+
+    def get(name, lit=False, w=W, h=H):
+        key = (name, lit, w, h)
+        if key not in cache:
+            hs = gpu.HostScene(name, lit=lit, synth_n=30)
+            cache[key] = (hs, hs.upload(w, h))
+        return cache[key][1]
+    yield get
+    for _, ds in cache.values():
+        ds.destroy()
+
+
+@pytest.mark.parametrize("name", ALL)
+@pytest.mark.parametrize("prec", ["f64", "f32", "mixed"])
+def test_trace_bit_exact(gpu, O, oracle_scene, dev_scene, name, prec):
+    """K1: hit flag, primitive ref, material, frontFace, t, p, normal and the ordered visit log are bit-identical."""
+    gp, op = {"f64": (gpu.PREC_F64, O.PREC_F64), "f32": (gpu.PREC_F32, O.PREC_F32), "mixed": (gpu.PREC_MIXED, O.PREC_MIXED)}[prec]
+    osc = oracle_scene(name)
+    rays = _rays(O, osc)
+    if prec != "f64":
+        rays = rays.astype(np.float32).astype(np.float64)
+    g = dev_scene(name).trace(rays, precision=gp, seed=9, log_stride=48)
+    o = osc.trace(rays, prec=op, seed=9, log_stride=48)
+    media = name in ("cornell_smoke", "next_week_final")
+    if media:
+        # media draw xi inside `hit` and use log(xi): libm and CUDA log differ in the last ulp for a few arguments, which moves t
+        # by an ulp; the visit ORDER must still agree everywhere, the values for all but a handful of rays
+        assert np.array_equal(g["nvisit"], o["nvisit"]) and np.array_equal(g["vhash"], o["vhash"])
+        same = (g["hit"] == o["hit"]) & (g["prim"] == o["prim"]) & (g["rec"][:, 0] == o["rec"][:, 0])
+        assert same.mean() > (0.995 if prec == "f64" else 0.97), same.mean()
+        return
+    assert np.array_equal(g["hit"], o["hit"])
+    assert np.array_equal(g["prim"], o["prim"]) and np.array_equal(g["mat"], o["mat"]) and np.array_equal(g["front"], o["front"])
+    assert np.array_equal(g["nvisit"], o["nvisit"]) and np.array_equal(g["vhash"], o["vhash"]) and np.array_equal(g["vlog"], o["vlog"])
+    assert np.array_equal(g["rec"][:, :7], o["rec"][:, :7])  # t, p, normal: only + - * / sqrt
+    # u, v involve atan2 / asin: libm vs CUDA, last-ulp differences allowed
+    tol = 1e-12 if prec == "f64" else 1e-5
+    assert np.allclose(g["rec"][:, 7:], o["rec"][:, 7:], atol=tol, rtol=0)
+    assert g["hit"].sum() > 100
+
+
+@pytest.mark.parametrize("name", NO_MEDIA)
+def test_fp32_traversal_agrees_with_reference_double(gpu, O, oracle_scene, dev_scene, name):
+    """fp32 device traversal vs the reference's Double arithmetic: agreement rate of hit id and visit order (grazing rays differ)."""
+    osc = oracle_scene(name)
+    rays = _rays(O, osc).astype(np.float32).astype(np.float64)
+    g = dev_scene(name).trace(rays, precision=gpu.PREC_F32, log_stride=0)
+    o = osc.trace(rays, prec=O.PREC_F64, log_stride=0)
+    assert ((g["hit"] == o["hit"]) & (g["prim"] == o["prim"])).mean() > 0.998
+    assert (g["vhash"] == o["vhash"]).mean() > 0.99
+
+
+@pytest.mark.parametrize("name", NO_MEDIA)
+def test_fast_math_traversal_agreement(gpu, O, oracle_scene, dev_scene, name):
+    """RT_FLAG_FAST_MATH (FMA contraction + reciprocal slab test) is not bit-exact; quantify it."""
+    osc = oracle_scene(name)
+    rays = _rays(O, osc).astype(np.float32).astype(np.float64)
+    g = dev_scene(name).trace(rays, precision=gpu.PREC_F32, flags=gpu.FLAG_FAST_MATH)
+    o = osc.trace(rays, prec=O.PREC_F32)
+    assert ((g["hit"] == o["hit"]) & (g["prim"] == o["prim"])).mean() > 0.999
+    assert (g["vhash"] == o["vhash"]).mean() > 0.995
+
+
+def _cmp_images(img, ref, frac_min=0.90, mean_tol=0.02):
+    nan_g, nan_r = np.isnan(img).any(axis=2), np.isnan(ref).any(axis=2)
+    # NaN masks (HEAD's 0/0 mixture pdf) must agree except where a path diverged
+    assert (nan_g == nan_r).mean() > 0.97, (nan_g.sum(), nan_r.sum())
+    ok = ~(nan_g | nan_r)
+    if ok.sum() == 0:
+        return
+    a, b = img[ok], ref[ok]
+    rel = np.abs(a - b) / (np.abs(b) + 1e-3)
+    frac = (rel < 1e-3).mean()
+    assert frac > frac_min, frac
+    assert abs(a.mean() - b.mean()) <= mean_tol * abs(b.mean()) + 1e-6, (a.mean(), b.mean())
+
+
+@pytest.mark.parametrize("name,lit", [(n, False) for n in ALL] + [(n, True) for n in ALL if n not in ("cornell", "cornell_smoke", "synthetic")])
+def test_render_matches_oracle_same_streams(gpu, O, oracle_scene, dev_scene, name, lit):
+    """K2 fp32 vs oracle<float>, identical per-(pixel,sample) streams, 8 spp, depth 50."""
+    spp = 8
+    img, st = dev_scene(name, lit).render(W, H, spp, depth=50, seed=21)
+    ref, _ = oracle_scene(name, lit).render(W, H, spp, depth=50, prec=O.PREC_F32, mode=1, seed=21)
+    assert st["samples"] == W * H * spp and st["launches"] == 1
+    media = name in ("cornell_smoke", "next_week_final")
+    _cmp_images(img, ref, frac_min=0.80 if media else 0.90, mean_tol=0.04 if media else 0.02)
+
+
+@pytest.mark.parametrize("name", ["cornell", "random", "next_week_final"])
+def test_render_fp64_matches_reference_arithmetic(gpu, O, oracle_scene, dev_scene, name):
+    """K2 in fp64 vs oracle<double> — the reference's own arithmetic — same streams."""
+    lit = name != "cornell"
+    img, _ = dev_scene(name, lit).render(W, H, 4, depth=50, seed=33, precision=gpu.PREC_F64)
+    ref, _ = oracle_scene(name, lit).render(W, H, 4, depth=50, prec=O.PREC_F64, mode=1, seed=33)
+    _cmp_images(img, ref, frac_min=0.85 if name == "next_week_final" else 0.93, mean_tol=0.03)
+
+
+@pytest.mark.parametrize("name", ["cornell", "two_perlin", "random_book1"])
+def test_fp32_radiance_vs_reference_double_converged(gpu, O, oracle_scene, dev_scene, name):
+    """fp32 GPU vs the reference's Double at matched spp, independent seeds: RMSE of the converged means must sit at the oracle's
+    own seed-to-seed noise floor (tolerance 1.25 x floor)."""
+    lit = name != "cornell"
+    spp = 256
+    w, h = 48, 32
+    hs = gpu.HostScene(name, lit=lit)
+    ds = hs.upload(w, h)
+    g, _ = ds.render(w, h, spp, seed=101)
+    ds.destroy()
+    osc = oracle_scene(name, lit)
+    a, _ = osc.render(w, h, spp, prec=O.PREC_F64, mode=1, seed=202)
+    b, _ = osc.render(w, h, spp, prec=O.PREC_F64, mode=1, seed=303)
+    # a light-sampled direction at the very edge of the sphere light's cone can miss it in htblPdfValue's re-trace, giving the
+    # HEAD estimator's 0/0 (Lib.hs:677-680, 1329-1333) in a handful of pixels, in the oracle as on the device: mask them out
+    ok = np.isfinite(g).all(axis=2) & np.isfinite(a).all(axis=2) & np.isfinite(b).all(axis=2)
+    assert ok.mean() > 0.97, ok.mean()
+    g, a, b = g[ok], a[ok], b[ok]
+    g, a, b = np.minimum(g / spp, 4.0), np.minimum(a / spp, 4.0), np.minimum(b / spp, 4.0)  # clip fireflies symmetrically
+    floor = np.sqrt(np.mean((a - b) ** 2))
+    rmse = 0.5 * (np.sqrt(np.mean((g - a) ** 2)) + np.sqrt(np.mean((g - b) ** 2)))
+    assert rmse < 1.25 * floor, (rmse, floor)
+    assert abs(g.mean() - 0.5 * (a.mean() + b.mean())) < 0.03 * a.mean()
+
+
+def test_counters_equal_oracle_traversal_counts(gpu, O, oracle_scene, dev_scene):
+    """The algorithmic-work counters behind the roofline (box tests, primitive tests, bounces ...) are the oracle's, exactly, when
+    every path coincides; scenes without transcendentals on the path (two_spheres lit is not one) so compare within 1 %."""
+    for name, lit in (("cornell", False), ("random_book1", True)):
+        _, st = dev_scene(name, lit).render(W, H, 4, counted=True, seed=77)
+        _, os_ = oracle_scene(name, lit).render(W, H, 4, prec=O.PREC_F32, mode=1, seed=77, stats=True)
+        c = st["counters"]
+        assert c["paths"] == os_["paths"] == W * H * 4
+        for k in ("bounces", "box_tests", "sphere_tests", "rect_tests", "cuboid_tests", "queries", "visits", "sphere_hits"):
+            assert abs(c[k] - os_[k]) <= 0.01 * os_[k] + 2, (name, k, c[k], os_[k])
+
+
+def test_sharding_invariance(gpu, dev_scene):
+    """Sample-range and region splits (what multi-GPU sharding does) reproduce the single-call image to double round-off."""
+    ds = dev_scene("cornell")
+    full, _ = ds.render(W, H, 12, seed=5)
+    a, _ = ds.render(W, H, 5, seed=5, s0=0)
+    b, _ = ds.render(W, H, 7, seed=5, s0=5)
+    assert np.allclose(a + b, full, rtol=1e-12, atol=1e-12)
+    top = np.zeros((H, W, 3)); ds.render(W, H, 12, seed=5, region=(0, 17, 0, W), out=top)
+    bot = np.zeros((H, W, 3)); ds.render(W, H, 12, seed=5, region=(17, H, 0, W), out=bot)
+    assert np.all(top[17:] == 0) and np.all(bot[:17] == 0)
+    assert np.allclose(top + bot, full, rtol=1e-12, atol=1e-12)
+    left = np.zeros((H, W, 3)); ds.render(W, H, 12, seed=5, region=(3, 30, 10, 41), out=left)
+    assert np.allclose(left[3:30, 10:41], full[3:30, 10:41], rtol=1e-12, atol=1e-12) and left[:3].sum() == 0 and left[:, :10].sum() == 0
+    again, _ = ds.render(W, H, 12, seed=5)
+    assert np.allclose(again, full, rtol=1e-12, atol=1e-12)
+    other, _ = ds.render(W, H, 12, seed=6)
+    assert not np.allclose(other, full)
+
+
+def test_edge_cases(gpu, dev_scene):
+    ds = dev_scene("cornell")
+    img, st = ds.render(W, H, 0)
+    assert st["launches"] == 0 and np.all(img == 0)
+    img, _ = ds.render(W, H, 3, depth=0)  # rayColor with depth <= 0 is black (Lib.hs:1303-1304)
+    assert np.all(img == 0)
+    img, _ = ds.render(W, H, 2, depth=1)  # one bounce: only directly visible emitters (back face) contribute
+    assert np.isfinite(img).all() and img.max() <= 2 * 15.0 + 1e-6
+    with pytest.raises(RuntimeError, match="bad region"):
+        ds.render(W, H, 1, region=(10, 5, 0, W))
+    img, _ = ds.render(1, 1, 7)  # ragged: a single pixel, fewer paths than one warp
+    assert img.shape == (1, 1, 3) and np.isfinite(img).all()
+
+
+@pytest.mark.parametrize("name,tex_kind", [("two_spheres", 1), ("two_perlin", 2), ("earth", 3), ("next_week_final", 2)])
+def test_texture_value(gpu, O, oracle_scene, dev_scene, name, tex_kind):
+    """textureValue probe: checker / Perlin marble (turb depth 7) / image lookup vs the oracle."""
+    hs = gpu.HostScene(name, synth_n=30)
+    d = gpu.desc_arrays(hs.desc(W, H).contents)
+    tex = int(np.nonzero(d["tex_kind"] == tex_kind)[0][0])
+    rng = np.random.default_rng(3)
+    q = np.concatenate([rng.random((4000, 2)), rng.normal(size=(4000, 3)) * 50], 1)
+    q[:8, :2] = [[0, 0], [1, 1], [0, 1], [1, 0], [0.5, 0.5], [0.999999, 1e-9], [1e-9, 0.999999], [0.25, 0.75]]
+    ds = dev_scene(name)
+    g64 = ds.texture_value(tex, q, precision=gpu.PREC_F64)
+    o64 = oracle_scene(name).texture_value(tex, q, prec=O.PREC_F64)
+    if tex_kind == 3:
+        assert np.array_equal(g64, o64)  # integer texel fetch / 255
+    elif tex_kind == 1:
+        assert (np.abs(g64 - o64).max(axis=1) == 0).mean() > 0.999  # sign of a product of sines
+    else:
+        assert np.allclose(g64, o64, atol=1e-9)
+    q32 = q.astype(np.float32).astype(np.float64)
+    g32 = ds.texture_value(tex, q32, precision=gpu.PREC_F32)
+    o32 = oracle_scene(name).texture_value(tex, q32, prec=O.PREC_F32)
+    if tex_kind == 2:
+        assert np.allclose(g32, o32, atol=2e-3)  # sin(z + 10*turb) in float amplifies ulps of the sum
+    else:
+        assert (np.abs(g32 - o32).max(axis=1) < 1e-6).mean() > 0.999
+
+
+def test_tonemap_and_run_render(gpu, O, oracle_scene):
+    """albedoToColor on the device == the oracle's; runRender through the mirrored host API returns the same 8-bit rows as
+    rt_render + albedoToColor."""
+    from ray_tracing_b200._scene import tonemap
+    x = np.concatenate([np.linspace(0, 1.2, 1000), [np.nan, -1.0, 1e30, 0.0]]) * 16
+    assert np.array_equal(tonemap(x, 16), O.albedo_to_color(x / 16))
+    hs = gpu.HostScene("cornell")
+    rgb = hs.run_render(32, 32, 16, 50)
+    ds = hs.upload(32, 32)
+    seed = int(O.splitmix(0, 1)[0][0])  # not the seed runRender used; recompute it the way Lib.cpp does: genWord64(g1)
+    g1 = hs.g1()
+    M = (1 << 64) - 1
+    s = (int(g1[0]) + int(g1[1])) & M
+    z = ((s ^ (s >> 33)) * 0xff51afd7ed558ccd) & M; z = ((z ^ (z >> 33)) * 0xc4ceb9fe1a85ec53) & M; seed = z ^ (z >> 33)
+    img, _ = ds.render(32, 32, 16, depth=50, seed=seed)
+    ds.destroy()
+    assert np.array_equal(rgb, O.albedo_to_color(img / 16))
+
+
+def test_cornell_matches_reference_png(gpu):
+    """Config 4 against the reference's own cornellBox1000.png (box-filtered fixture), through the product path."""
+    import os
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cornellBox1000_box4.npy"))
+    hs = gpu.HostScene("cornell")
+    rgb = hs.run_render(125, 125, 1000, 50).astype(np.float32)
+    for ch in range(3):
+        assert abs(rgb[..., ch].mean() - gold[..., ch].mean()) < 1.0, (ch, rgb[..., ch].mean(), gold[..., ch].mean())
+    a = rgb.reshape(25, 5, 25, 5, 3).mean(axis=(1, 3)); b = gold.reshape(25, 5, 25, 5, 3).mean(axis=(1, 3))
+    assert np.sqrt(np.mean((a - b) ** 2)) < 5.0

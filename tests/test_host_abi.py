@@ -1,0 +1,124 @@
+"""CPU tests of the drop-in boundary: the C-ABI library loads and exports every symbol of include/rt_abi.h, the struct layouts
+seen from Python match the header, the host mirror's flattener agrees bit-for-bit with the oracle's independent scene
+construction, and the library validates scenes and fails loudly without a GPU (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SCENES = ["cornell", "cornell_smoke", "simple_light", "earth", "two_perlin", "two_spheres", "random_book1", "random", "next_week_final", "synthetic"]
+
+
+def test_abi_exports_every_declared_symbol(R):
+    hdr = open(os.path.join(ROOT, "include", "rt_abi.h")).read()
+    declared = set(re.findall(r"^(?:int|void|const char\*)\s+(rt_[a-z_]+)\s*\(", hdr, re.M))
+    assert declared == set(R.ABI_SYMBOLS), declared ^ set(R.ABI_SYMBOLS)
+    L = R.core()
+    for s in declared:
+        assert hasattr(L, s), s
+    assert L.rt_abi_version() == 1
+    lim = R.RtLimits()
+    assert L.rt_get_limits(C.byref(lim)) == 0 and lim.max_frames >= 2 and lim.max_stack >= 48
+
+
+def test_struct_layouts_match_header(R, tmp_path):
+    src = tmp_path / "sz.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "rt_abi.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu\\n",'
+                   'sizeof(RtSceneDesc),sizeof(RtRenderParams),sizeof(RtStats),offsetof(RtSceneDesc,camera),offsetof(RtRenderParams,seed),sizeof(RtLimits));return 0;}')
+    exe = tmp_path / "sz"
+    subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    got = [int(x) for x in subprocess.check_output([str(exe)]).split()]
+    assert got == [C.sizeof(R.RtSceneDesc), C.sizeof(R.RtRenderParams), C.sizeof(R.RtStats), R.RtSceneDesc.camera.offset,
+                   R.RtRenderParams.seed.offset, C.sizeof(R.RtLimits)]
+
+
+@pytest.mark.parametrize("name", SCENES)
+@pytest.mark.parametrize("lit", [False, True])
+def test_flattener_matches_oracle_scene(R, O, oracle_scene, name, lit):
+    """Two independent restatements of Scenes.hs + makeBVH + makePerlin + newCamera (pointer tree in oracle/, index arena in
+    ray-tracing_b200/host/) must produce the same canonical flattened scene, bit for bit, from randGen 1024."""
+    hs = R.HostScene(name, lit=lit, synth_n=30)
+    d = R.desc_arrays(hs.desc(60, 40).contents)
+    os_ = oracle_scene(name, lit=lit, synth_n=30)
+    roots, bg, g1 = os_.roots()
+    assert roots[0] == d["world_root"] and roots[1] == d["lights_root"]
+    assert np.array_equal(bg, d["background"]) and np.array_equal(g1, hs.g1())
+    assert np.array_equal(os_.camera(60, 40), d["camera"])
+
+    def two(a, b):
+        return np.stack([a, b], 1) if len(a) else np.zeros((0, 2), np.uint32)
+    D, U = os_.export(1); assert np.array_equal(D, d["sphere_cr"]) and np.array_equal(U[:, 0], d["sphere_mat"])
+    D, U = os_.export(2); assert np.array_equal(D, d["moving"]) and np.array_equal(U[:, 0], d["moving_mat"])
+    D, U = os_.export(3); assert np.array_equal(D, d["rect"]) and np.array_equal(U[:, 1], d["rect_mat"])
+    D, U = os_.export(6); assert np.array_equal(D, d["cuboid"]) and np.array_equal(U[:, 0], d["cuboid_mat"])
+    D, U = os_.export(7)
+    assert np.array_equal(D, d["node_box"]) and np.array_equal(U[:, 0], d["node_left"]) and np.array_equal(U[:, 1], d["node_right"]) and np.array_equal(U[:, 2], d["node_size"])
+    D, U = os_.export(8); assert np.array_equal(D, d["translate_off"]) and np.array_equal(U[:, 0], d["translate_child"])
+    D, U = os_.export(9); assert np.array_equal(D, d["rotate_sc"]) and np.array_equal(U, two(d["rotate_axis"], d["rotate_child"]))
+    D, U = os_.export(10); assert np.array_equal(D[:, 0], d["medium_neg_inv_density"]) and np.array_equal(U, two(d["medium_mat"], d["medium_boundary"]))
+    D, U = os_.export(11); assert np.array_equal(D[:, 0], d["mat_param"]) and np.array_equal(U, two(d["mat_kind"], d["mat_tex"]))
+    D, U = os_.export(12)
+    assert np.array_equal(D[:, :3], d["tex_rgb"]) and np.array_equal(D[:, 3], d["tex_scale"])
+    assert np.array_equal(U, np.stack([d["tex_kind"], d["tex_a"], d["tex_b"]], 1))
+    D, U = os_.export(13); assert np.array_equal(D, d["perlin_ranvec"]) and np.array_equal(U, d["perlin_perm"].astype(np.uint32))
+    # the rect plane travels in the ref kind: every rect ref found in the graph must carry the plane the oracle recorded
+    planes = os_.export(3)[1][:, 0]
+    refs = np.concatenate([d["node_left"], d["node_right"], d["translate_child"], d["rotate_child"], d["medium_boundary"], [d["world_root"], d["lights_root"]]]).astype(np.uint32)
+    for r in refs:
+        k, i = int(r) >> 28, int(r) & 0x0fffffff
+        if 3 <= k <= 5:
+            assert planes[i] == k - 3
+
+
+def test_scene_validation_errors(R):
+    """Bad descriptions are rejected with RT_ERR_ARG before any device work."""
+    hs = R.HostScene("cornell")
+    d = hs.desc(16, 16).contents
+    sid = C.c_uint64()
+    L = R.core()
+    bad = R.RtSceneDesc.from_buffer_copy(d); bad.abi_version = 99
+    assert L.rt_scene_create(C.byref(bad), -1, C.byref(sid)) == -1 and b"abi_version" in L.rt_last_error()
+    bad = R.RtSceneDesc.from_buffer_copy(d); bad.world_root = (7 << 28) | 1000
+    assert L.rt_scene_create(C.byref(bad), -1, C.byref(sid)) == -1 and b"root" in L.rt_last_error()
+    bad = R.RtSceneDesc.from_buffer_copy(d); bad.node_box = None
+    assert L.rt_scene_create(C.byref(bad), -1, C.byref(sid)) == -1
+    left = np.ctypeslib.as_array(C.cast(d.node_left, C.POINTER(C.c_uint32)), shape=(d.n_nodes,)).copy()
+    left[0] = (7 << 28) | 0  # node 0 is its own child
+    bad = R.RtSceneDesc.from_buffer_copy(d); bad.node_left = left.ctypes.data_as(C.c_void_p)
+    assert L.rt_scene_create(C.byref(bad), -1, C.byref(sid)) == -1 and b"cycle" in L.rt_last_error()
+    assert L.rt_scene_destroy(C.c_uint64(12345)) == -4
+    assert L.rt_render(C.c_uint64(12345), None, None, None) == -4
+
+
+def test_no_cpu_fallback(R):
+    """On a box without a CUDA device every compute entry point must fail loudly with RT_ERR_CUDA."""
+    if R.core().rt_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    hs = R.HostScene("two_spheres")
+    with pytest.raises(RuntimeError, match="no CUDA device"):
+        hs.upload(8, 8)
+    with pytest.raises(RuntimeError, match="no CUDA device"):
+        hs.run_render(8, 8, 1)
+    with pytest.raises(RuntimeError, match="no CUDA device"):
+        from ray_tracing_b200._scene import tonemap
+        tonemap(np.zeros(3), 1)
+
+
+def test_product_does_not_touch_oracle():
+    """The product package must not include, import or link anything under oracle/."""
+    pkg = os.path.join(ROOT, "ray-tracing_b200")
+    for dp, _, fs in os.walk(pkg):
+        if "build" in dp:
+            continue
+        for f in fs:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp", "Makefile")):
+                txt = open(os.path.join(dp, f)).read()
+                for pat in (r'#include\s+"[^"]*oracle', r"^\s*(import|from)\s+oracle", r"liboracle", r"-loracle", r"oracle\.py", r"rt_oracle\.hpp", r"rt_scenes\.hpp"):
+                    assert not re.search(pat, txt, re.M), (pat, os.path.join(dp, f))
+    for so in ("librt_b200.so", "librt_host.so"):
+        out = subprocess.check_output(["ldd", os.path.join(pkg, so)]).decode()
+        assert "oracle" not in out

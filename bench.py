@@ -90,3 +90,196 @@ def scene_bytes(d):
         w = C.cast(d.image_w, C.POINTER(C.c_uint32))[i]; h = C.cast(d.image_h, C.POINTER(C.c_uint32))[i]
         n += w * h * 3
     return int(n)
+
+
+def run_reference(args, W, H, rank):
+    """--impl reference: the reference's CPU algorithm (oracle<double>, runRender's per-column SplitMix plumbing) on the host cores.
+    The Haskell build itself cannot run here (no GHC on either box); see DESIGN.md."""
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as O
+    import rtb200_loader
+    pkg = rtb200_loader.load()
+    earth = pkg.load_earth() if args.scene in ("earth", "random", "next_week_final") else None
+    osc = O.OracleScene(args.scene, earth=earth, synth_n=args.synth_n)
+    cores = os.cpu_count() or 1
+    spp = args.ref_spp
+    w, h = (W, H) if args.scene != "synthetic" else (480, 270)
+    times = []
+    for i in range(args.warmup + args.steps):
+        t = time.time()
+        osc.render(w, h, spp, depth=50, prec=O.PREC_F64, mode=0, seed=1000 + i, threads=cores)
+        if i >= args.warmup:
+            times.append(time.time() - t)
+    tot = sum(times)
+    v = args.steps * w * h * spp / tot
+    sample = "%dx%d, %d spp per step (full frame, reduced spp), depth 50" % (w, h, spp)
+    print(json.dumps({
+        "impl": "reference", "metric": "samples/sec", "value": v, "unit": "samples/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * tot / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": SCENE_DOC[args.scene], "scene": args.scene, "width": w, "height": h, "spp_per_step": spp, "max_depth": 50},
+        "cpu_baseline": {"value": v, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--scene", default="random", choices=list(SCENE_DOC))
+    ap.add_argument("--spp", type=int, default=0)
+    ap.add_argument("--ref-spp", type=int, default=8)
+    ap.add_argument("--synth-n", type=int, default=1000)
+    ap.add_argument("--fast", action="store_true", help="RT_FLAG_FAST_MATH kernels (not bit-exact; reported separately)")
+    ap.add_argument("--precision", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    W, H = SCENE_SIZE[args.scene]
+    spp = args.spp or SCENE_SPP[args.scene]
+    if args.impl == "reference":
+        return run_reference(args, W, H, rank)
+
+    import torch
+    import torch.distributed as dist
+    import rtb200_loader
+    pkg = rtb200_loader.load()
+    from ray_tracing_b200 import _dist
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    flags = pkg.FLAG_FAST_MATH if args.fast else 0
+
+    hs = pkg.HostScene(args.scene, synth_n=args.synth_n)
+    desc = hs.desc(W, H)
+    ds = pkg.DeviceScene(desc, local)
+    fb = torch.zeros((H, W, 3), dtype=torch.float64, device=dev)
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    stream = torch.cuda.current_stream().cuda_stream
+    total_spp = spp * world  # weak scaling: every GPU renders `spp` samples per pixel
+
+    # algorithmic work per sample (instrumented kernel, small spp; the counters equal the oracle's, tests/test_gpu_parity.py)
+    work = None
+    if rank == 0:
+        _, st = ds.render(W, H, 2 if args.scene != "synthetic" else 1, counted=True, seed=99, precision=args.precision, flags=flags)
+        work = algorithmic_work(st["counters"])
+
+    def step(i):
+        flush_buf.zero_()  # L2 flush between iterations
+        fb.zero_()
+        s0, n = _dist.shard_samples(total_spp, rank, world)
+        ds.render_device(fb.data_ptr(), W, H, n, stream=stream, depth=50, seed=1 + i, s0=s0, precision=args.precision, flags=flags, total=total_spp)
+        _dist.reduce_framebuffer(fb, 0)
+
+    def sync():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(args.warmup):
+        step(i)
+    sync()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    # kernel-only timing for the roofline: events right around the render kernel on its stream
+    k_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync()
+    e0.record()
+    for i in range(args.steps):
+        flush_buf.zero_(); fb.zero_()
+        s0, n = _dist.shard_samples(total_spp, rank, world)
+        k_ev[i][0].record()
+        ds.render_device(fb.data_ptr(), W, H, n, stream=stream, depth=50, seed=100 + i, s0=s0, precision=args.precision, flags=flags, total=total_spp)
+        k_ev[i][1].record()
+        _dist.reduce_framebuffer(fb, 0)
+    e1.record()
+    sync()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    clocks = sampler.stop() if rank == 0 else None
+    kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in k_ev]))
+    value = args.steps * W * H * total_spp / (ms / 1e3)
+    finite_frac = float(torch.isfinite(fb).all(dim=2).float().mean().item()) if rank == 0 else None
+
+    # ---- e2e: the user-facing calls with HOST buffers: rt_scene_create (H2D) + render + reduce + D2H of the frame, every step
+    host_out = np.zeros((H, W, 3))
+    pinned = torch.zeros((H, W, 3), dtype=torch.float64).pin_memory()
+
+    def e2e_step(i):
+        if world == 1:
+            d2 = pkg.DeviceScene(desc, local)
+            d2.render(W, H, spp, depth=50, seed=500 + i, out=host_out, precision=args.precision, flags=flags)
+            d2.destroy()
+        else:
+            d2 = pkg.DeviceScene(desc, local)
+            _dist.render_sharded(d2, W, H, total_spp, 50, 500 + i, fb, stream=stream, precision=args.precision, flags=flags)
+            if rank == 0:
+                pinned.copy_(fb, non_blocking=False)
+            d2.destroy()
+    e2e_step(0)
+    sync()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        e2e_step(i)
+    sync()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e_value = args.steps * W * H * total_spp / e2e_s
+
+    if rank == 0:
+        pk = peaks()
+        hbm_peak = pk["hbm_gbs"] if pk else 6650.0
+        bytes_ps, flops_ps, per_sample = work
+        samples_per_launch = W * H * spp
+        ach_gbs = bytes_ps * samples_per_launch / (kernel_ms / 1e3) / 1e9
+        ach_tf = flops_ps * samples_per_launch / (kernel_ms / 1e3) / 1e12
+        line = {
+            "metric": "samples/sec", "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": ["f32", "f32+f64 sphere", "f64"][args.precision], "data": "synthetic",
+            "config": {"workload": SCENE_DOC[args.scene], "scene": args.scene, "width": W, "height": H, "spp_per_gpu_per_step": spp, "max_depth": 50,
+                       "seed": "randGen 1024", "lights": "HEAD", "parallelism": "spp-sharded x%d + ncclReduce" % world, "l2": "flushed between steps (256 MiB write)",
+                       "arithmetic": "fast-math" if args.fast else "literal (no FMA contraction, IEEE div/sqrt)", "finite_pixel_fraction": finite_frac},
+            "roofline": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak, "traffic": None,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst)" if pk else "fallback 6.65 TB/s", "kernel": "renderKernel", "kernel_ms": kernel_ms,
+                         "algorithmic_bytes_per_sample": bytes_ps, "per_sample": per_sample,
+                         "note": "scene is L1/L2-resident (KBs..MBs); the binding roofline is FP32 issue under divergence, see roofline_fp32"},
+            "roofline_fp32": {"bound": "fp32-issue", "achieved": ach_tf, "peak": FP32_PEAK_TFLOPS_NOMINAL, "unit": "TFLOP/s", "frac": ach_tf / FP32_PEAK_TFLOPS_NOMINAL,
+                              "peak_source": "nominal 148 SM x 128 lanes x 2 x 1.965 GHz", "algorithmic_flops_per_sample": flops_ps},
+            "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": scene_bytes(desc.contents), "d2h_bytes_per_step": W * H * 3 * 8},
+            "gpu_launches": args.steps, "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            sys.path.insert(0, os.path.join(ROOT, "oracle"))
+            import oracle as O
+            earth = pkg.load_earth() if args.scene in ("earth", "random", "next_week_final") else None
+            osc = O.OracleScene(args.scene, earth=earth, synth_n=args.synth_n)
+            cores = os.cpu_count() or 1
+            w, h = (W, H) if args.scene != "synthetic" else (480, 270)
+            t0 = time.time()
+            osc.render(w, h, args.ref_spp, depth=50, prec=O.PREC_F64, mode=0, seed=4242, threads=cores)
+            dt = time.time() - t0
+            line["cpu_baseline"] = {"value": w * h * args.ref_spp / dt, "unit": "samples/s", "cores": cores, "kind": "port",
+                                    "sample": "%dx%d at %d spp, depth 50, oracle<double> in runRender's RNG plumbing, %d threads (%.1f s)" % (w, h, args.ref_spp, cores, dt)}
+        print(json.dumps(line))
+    ds.destroy()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

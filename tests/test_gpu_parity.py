@@ -132,30 +132,34 @@ def test_render_fp64_matches_reference_arithmetic(gpu, O, oracle_scene, dev_scen
     _cmp_images(img, ref, frac_min=0.85 if name == "next_week_final" else 0.93, mean_tol=0.03)
 
 
-@pytest.mark.parametrize("name", ["cornell", "two_perlin", "random_book1"])
-def test_fp32_radiance_vs_reference_double_converged(gpu, O, oracle_scene, dev_scene, name):
-    """fp32 GPU vs the reference's Double at matched spp, independent seeds: RMSE of the converged means must sit at the oracle's
-    own seed-to-seed noise floor (tolerance 1.25 x floor)."""
+@pytest.mark.parametrize("name", ["cornell", "simple_light", "random_book1"])
+def test_radiance_vs_reference_double_converged(gpu, O, oracle_scene, dev_scene, name):
+    """GPU vs the reference's Double at matched spp, independent seeds.  The production arithmetic (fp32 with the sphere quadratic
+    in fp64, RT_PREC_MIXED) must sit at the oracle's own seed-to-seed noise floor (RMSE of converged means <= 1.25 x floor, mean
+    within 1.5 %).  Pure fp32 is allowed the self-intersection darkening that a radius-1000 sphere causes with t_min = 1e-4
+    (Lib.hs:77,1309): mean within 5 %."""
     lit = name != "cornell"
     spp = 256
     w, h = 48, 32
     hs = gpu.HostScene(name, lit=lit)
     ds = hs.upload(w, h)
-    g, _ = ds.render(w, h, spp, seed=101)
+    gm, _ = ds.render(w, h, spp, seed=101, precision=gpu.PREC_MIXED)
+    gf, _ = ds.render(w, h, spp, seed=101, precision=gpu.PREC_F32)
     ds.destroy()
     osc = oracle_scene(name, lit)
     a, _ = osc.render(w, h, spp, prec=O.PREC_F64, mode=1, seed=202)
     b, _ = osc.render(w, h, spp, prec=O.PREC_F64, mode=1, seed=303)
     # a light-sampled direction at the very edge of the sphere light's cone can miss it in htblPdfValue's re-trace, giving the
     # HEAD estimator's 0/0 (Lib.hs:677-680, 1329-1333) in a handful of pixels, in the oracle as on the device: mask them out
-    ok = np.isfinite(g).all(axis=2) & np.isfinite(a).all(axis=2) & np.isfinite(b).all(axis=2)
+    ok = np.isfinite(gm).all(axis=2) & np.isfinite(gf).all(axis=2) & np.isfinite(a).all(axis=2) & np.isfinite(b).all(axis=2)
     assert ok.mean() > 0.97, ok.mean()
-    g, a, b = g[ok], a[ok], b[ok]
-    g, a, b = np.minimum(g / spp, 4.0), np.minimum(a / spp, 4.0), np.minimum(b / spp, 4.0)  # clip fireflies symmetrically
+    gm, gf, a, b = (np.minimum(x[ok] / spp, 4.0) for x in (gm, gf, a, b))  # clip fireflies symmetrically
     floor = np.sqrt(np.mean((a - b) ** 2))
-    rmse = 0.5 * (np.sqrt(np.mean((g - a) ** 2)) + np.sqrt(np.mean((g - b) ** 2)))
+    rmse = 0.5 * (np.sqrt(np.mean((gm - a) ** 2)) + np.sqrt(np.mean((gm - b) ** 2)))
+    ref_mean = 0.5 * (a.mean() + b.mean())
     assert rmse < 1.25 * floor, (rmse, floor)
-    assert abs(g.mean() - 0.5 * (a.mean() + b.mean())) < 0.03 * a.mean()
+    assert abs(gm.mean() - ref_mean) < 0.015 * ref_mean, (gm.mean(), ref_mean)
+    assert abs(gf.mean() - ref_mean) < 0.05 * ref_mean, (gf.mean(), ref_mean)
 
 
 def test_counters_equal_oracle_traversal_counts(gpu, O, oracle_scene, dev_scene):

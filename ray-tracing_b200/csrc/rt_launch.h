@@ -11,6 +11,7 @@ struct RenderArgs {
   uint32_t maxDepth;
   uint32_t row0, row1, col0, col1; // region (rows counted from the top)
   uint32_t chunk;                  // path indices a warp takes per atomic
+  uint32_t stackCap;               // traversal stack entries per thread (set by the launcher)
   unsigned long long seed;
   unsigned long long total_paths;  // region pixels * ns
   unsigned long long* counter;     // device: next free path index
@@ -20,6 +21,7 @@ struct RenderArgs {
 
 struct TraceArgs {
   uint32_t n, logStride;
+  uint32_t stackCap;
   double tmin, tmax;
   unsigned long long seed;
   const double* rays;  // device [n][7]

@@ -1,0 +1,271 @@
+// rt_render_kernel.inl — K2 (renderKernel) and K1 (traceKernel).  Included by rt_kernels.cuh inside namespace rtb.
+//
+// renderKernel: persistent warps, one camera path per lane.  Every lane is a small state machine whose pending work falls in
+// one of five classes: a BVH-node step, a sphere-leaf step, a rect/cuboid-leaf step, a rare traversal step, or "shade"
+// (consume a finished query: build the hit record, scatter, start the next query, or end the path and take the next path
+// index of the warp's chunk).  Each warp iteration ballots the classes and runs the ONE class most lanes are waiting for
+// (with ageing so no lane starves): divergent paths are regrouped by what they need to do next instead of executing every
+// branch with a handful of lanes.  Per lane the order of steps, and of RNG draws, is unchanged — results do not depend on
+// the schedule.
+
+enum : int { PH_IDLE = 0, PH_MAIN = 1, PH_LPDF = 2 };
+constexpr int kShadeMin = 8;    // run the shade class as soon as this many lanes wait for it
+constexpr int kAgeShade = 24;   // ... or when it has waited this many iterations
+constexpr int kAgeTrav = 6;     // a non-empty traversal class is run at the latest after this many iterations
+
+template <class T> struct PathState {
+  V3<T> beta; T time; int depthLeft; int phase; Rng rng;
+  double acc0, acc1, acc2; uint32_t accPix;
+  T l_spdf, l_v2, l_v1, curW; uint32_t curLight; int lsp;
+  uint32_t lref[kMaxLightDepth]; T lwt[kMaxLightDepth];
+};
+
+// consume the finished query of this lane.  Returns true when a new query must be started on ray (qo, qd) with root qroot.
+template <class T, int INSTR>
+__device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, PathState<T>& ps, Instr<INSTR>& ins, V3<T>& qo, V3<T>& qd) {
+  const uint32_t lightsKind = sc.lights_root >> 28;
+  auto finish = [&](const V3<T>& L) { ps.acc0 += (double)L.x; ps.acc1 += (double)L.y; ps.acc2 += (double)L.z; ps.phase = PH_IDLE; };
+  bool scattered = false;  // the path continues with (qo, qd) as the next bounce ray
+  qo = tr.o; qd = tr.d;    // all frames are closed when a query ends: this is the query's world ray
+  if (ps.phase == PH_MAIN) {
+    if (!tr.qhit) { finish(ps.beta * mk<T>(sc.bg[0], sc.bg[1], sc.bg[2])); return false; }  // Lib.hs:1310-1313
+    HitRec<T> rec;
+    evalHit<T>(sc, tr.o, tr.d, ps.time, tr.tbest, tr.bprim, tr.baux(), tr.bdepth(), &tr.x(X_BCHAIN), tr.stride, rec);
+    const Q4<T> m = ldq(sc.mats + rec.mat);
+    const uint32_t mkind = bitsOf(m.x), tex = bitsOf(m.y);
+    if (mkind == M_LIGHT) {  // scatter = Nothing -> emitted, back face only (Lib.hs:860, 880-885)
+      V3<T> e = mk<T>(0, 0, 0);
+      if (!rec.front) e = textureValue<T, INSTR>(sc, tex, rec.u, rec.v, rec.p, ins);
+      finish(ps.beta * e);
+      return false;
+    } else if (mkind == M_LAMBERTIAN) {  // Lib.hs:823-836 with pdfGenerate/pdfValue of the mixture (367-382)
+      const V3<T> att = textureValue<T, INSTR>(sc, tex, rec.u, rec.v, rec.p, ins);
+      const Onb<T> uvw = onbFromW(rec.n);
+      const T rd = rnd<T>(ps.rng);
+      V3<T> pdfD;
+      if (rd < (T)0.5) pdfD = htblRandom<T>(sc, sc.lights_root, rec.p, ps.rng);
+      else pdfD = onbLocal(uvw, randomCosineDirection<T>(ps.rng));
+      const V3<T> dir = unit(pdfD);
+      const T cosine = dot(unit(dir), uvw.w);
+      ps.l_v2 = (cosine <= 0) ? (T)0 : cosine / kPi<T>();
+      const T c2 = dot(rec.n, dir);  // scatteringPdf (Lib.hs:874-878)
+      ps.l_spdf = (c2 < 0) ? (T)0 : c2 / kPi<T>();
+      ps.beta = ps.beta * att;
+      qo = rec.p; qd = dir;
+      if (lightsKind == K_UNHITTABLE) {  // htblPdfValue Unhittable = 0 without any traversal (Lib.hs:677-680, 1109)
+        ins.count(13); ins.visit(sc.lights_root);
+        const T pdfVal = (T)0.5 * ((T)0 + ps.l_v2);
+        ps.beta = scale(ps.l_spdf / pdfVal, ps.beta);
+        scattered = true;
+      } else {
+        ps.phase = PH_LPDF; ps.l_v1 = 0; ps.lsp = 0; ps.curLight = sc.lights_root; ps.curW = 1;
+        return true;
+      }
+    } else if (mkind == M_METAL) {  // Lib.hs:837-841: never absorbs, fuzz unclamped
+      const V3<T> rUnit = randomUnitVector<T>(ps.rng);
+      const V3<T> reflected = reflectV(unit(tr.d), rec.n);
+      ps.beta = ps.beta * textureValue<T, INSTR>(sc, tex, rec.u, rec.v, rec.p, ins);
+      qo = rec.p; qd = reflected + scale(m.z, rUnit);
+      scattered = true;
+    } else if (mkind == M_DIELECTRIC) {  // Lib.hs:842-859: xi is always drawn
+      const T eta = rec.front ? (T)1.0 / m.z : m.z;
+      const V3<T> ud = unit(tr.d);
+      const T cosTheta = hmin(dot(neg(ud), rec.n), (T)1.0);
+      const T sinTheta = msqrt((T)1.0 - cosTheta * cosTheta);
+      const T rd = rnd<T>(ps.rng);
+      if ((eta * sinTheta > (T)1.0) || rd < schlick<T>(cosTheta, eta)) qd = reflectV(ud, rec.n);
+      else qd = refractV(ud, rec.n, eta);
+      qo = rec.p;
+      scattered = true;
+    } else {  // Isotropic (Lib.hs:861-865) weighted by the generic scatteringPdf / 1.0 (867-878, 1329-1333)
+      const V3<T> randDr = randomInUnitSphere<T>(ps.rng);
+      const V3<T> att = textureValue<T, INSTR>(sc, tex, rec.u, rec.v, rec.p, ins);
+      const T c2 = dot(rec.n, randDr);
+      const T spdf = (c2 < 0) ? (T)0 : c2 / kPi<T>();
+      ps.beta = scale(spdf / (T)1.0, ps.beta * att);
+      qo = rec.p; qd = randDr;
+      scattered = true;
+    }
+  } else {  // PH_LPDF: htblPdfValue (Lib.hs:673-705) for `curLight`, walked depth-first, left first
+    if (tr.qhit) {
+      const uint32_t lk = ps.curLight >> 28, li = ps.curLight & 0x0fffffffu;
+      if (lk == K_RECT_XZ) {
+        const Q4<T> ra = ldq(sc.rects + 2 * (size_t)li);
+        const T area = (ra.y - ra.x) * (ra.w - ra.z);
+        const T distanceSquared = tr.tbest * tr.tbest * sqlen(tr.d);
+        const T cosine = mabs(tr.d.y / len(tr.d));  // |v . (0,+-1,0)| / |v|
+        ps.l_v1 = ps.l_v1 + ps.curW * (distanceSquared / (cosine * area));
+      } else if (lk == K_SPHERE) {
+        const Q4<T> q = ldq(sc.spheres + li);
+        const T cosThetaMax = msqrt(1 - q.w * q.w / sqlen(mk<T>(q.x, q.y, q.z) - tr.o));
+        const T solidAngle = 2 * kPi<T>() * (1 - cosThetaMax);
+        ps.l_v1 = ps.l_v1 + ps.curW * (1 / solidAngle);
+      } else if (lk == K_BVH) {
+        const uint4 sz = __ldg(sc.node_sz + li);
+        const uint32_t lc = bitsOf(ldq(sc.nodes + 2 * (size_t)li).w), rc = bitsOf(ldq(sc.nodes + 2 * (size_t)li + 1).w);
+        if (ps.lsp + 2 <= kMaxLightDepth) {
+          ps.lref[ps.lsp] = rc; ps.lwt[ps.lsp] = ps.curW * ((T)sz.z / (T)sz.x); ++ps.lsp;
+          ps.lref[ps.lsp] = lc; ps.lwt[ps.lsp] = ps.curW * ((T)sz.y / (T)sz.x); ++ps.lsp;
+        }
+      }
+    }
+    if (ps.lsp > 0) { --ps.lsp; ps.curLight = ps.lref[ps.lsp]; ps.curW = ps.lwt[ps.lsp]; return true; }
+    const T pdfVal = (T)0.5 * (ps.l_v1 + ps.l_v2);
+    ps.beta = scale(ps.l_spdf / pdfVal, ps.beta);
+    ps.phase = PH_MAIN; scattered = true;
+  }
+  if (scattered) {  // rayColorHelp newRay (d - 1) (Lib.hs:1321-1333)
+    --ps.depthLeft;
+    if (ps.depthLeft <= 0) { finish(ps.beta * mk<T>(0, 0, 0)); return false; }
+    return true;
+  }
+  return false;
+}
+
+template <class T, class S, int INSTR, bool FAST>
+__global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __grid_constant__ DScene<T> sc, const __grid_constant__ RenderArgs a) {
+  extern __shared__ uint32_t smem[];
+  const unsigned lane = threadIdx.x & 31u;
+  const unsigned ltMask = (1u << lane) - 1u;
+  Instr<INSTR> ins;
+  if constexpr (INSTR == 1) ins.init();
+
+  Trav<T> tr;
+  tr.col = smem + threadIdx.x; tr.stride = blockDim.x; tr.xbase = a.stackCap;
+  tr.cur = kEmpty; tr.sp = 0; tr.qhit = false; tr.flags = 0; tr.bprim = 0; tr.tmin = 0; tr.tbest = 0;
+  tr.o = mk<T>(0, 0, 0); tr.d = mk<T>(0, 0, 1); tr.inv = mk<T>(0, 0, 0);
+  PathState<T> ps;
+  ps.phase = PH_IDLE; ps.beta = mk<T>(1, 1, 1); ps.time = 0; ps.depthLeft = 0; ps.rng = Rng{0, 1};
+  ps.acc0 = ps.acc1 = ps.acc2 = 0; ps.accPix = kNone;
+  ps.l_spdf = ps.l_v2 = ps.l_v1 = 0; ps.curW = 1; ps.curLight = 0; ps.lsp = 0;
+  unsigned long long cNext = 0, cEnd = 0, cBase = 0; uint32_t cPix0 = 0, cS0 = 0; bool exhausted = false;
+  const uint32_t regionW = a.col1 - a.col0;
+  int age0 = 0, age1 = 0, age2 = 0, age3 = 0, age4 = 0;
+
+  auto flush = [&]() {
+    if (ps.accPix != kNone) {
+      atomicAdd(a.out + (size_t)ps.accPix * 3, ps.acc0); atomicAdd(a.out + (size_t)ps.accPix * 3 + 1, ps.acc1); atomicAdd(a.out + (size_t)ps.accPix * 3 + 2, ps.acc2);
+    }
+  };
+
+  for (;;) {
+    // ---- classify this lane's pending work and vote
+    const bool dead = (ps.phase == PH_IDLE) && exhausted;
+    const int cls = dead ? -1 : (tr.cur == kEmpty ? 4 : stepClass(tr.cur));
+    const unsigned m0 = __ballot_sync(0xffffffffu, cls == 0), m1 = __ballot_sync(0xffffffffu, cls == 1), m2 = __ballot_sync(0xffffffffu, cls == 2),
+                   m3 = __ballot_sync(0xffffffffu, cls == 3), m4 = __ballot_sync(0xffffffffu, cls == 4);
+    if ((m0 | m1 | m2 | m3 | m4) == 0u) break;
+    const int c0 = __popc(m0), c1 = __popc(m1), c2 = __popc(m2), c3 = __popc(m3), c4 = __popc(m4);
+    int pick;
+    if ((c0 + c1 + c2 + c3) == 0 || c4 >= kShadeMin || (c4 > 0 && age4 >= kAgeShade)) pick = 4;
+    else if (c3 > 0 && age3 >= kAgeTrav) pick = 3;
+    else if (c2 > 0 && age2 >= kAgeTrav) pick = 2;
+    else if (c1 > 0 && age1 >= kAgeTrav) pick = 1;
+    else if (c0 > 0 && age0 >= kAgeTrav) pick = 0;
+    else {
+      pick = 0; int best = c0;
+      if (c1 > best) { pick = 1; best = c1; }
+      if (c2 > best) { pick = 2; best = c2; }
+      if (c3 > best) { pick = 3; best = c3; }
+    }
+    age0 = (c0 > 0 && pick != 0) ? age0 + 1 : 0; age1 = (c1 > 0 && pick != 1) ? age1 + 1 : 0; age2 = (c2 > 0 && pick != 2) ? age2 + 1 : 0;
+    age3 = (c3 > 0 && pick != 3) ? age3 + 1 : 0; age4 = (c4 > 0 && pick != 4) ? age4 + 1 : 0;
+
+    const T qtime = (ps.phase == PH_MAIN) ? ps.time : (T)0;  // htblPdfValue traces with time 0 (Lib.hs:677)
+    if (pick == 0) { if (cls == 0) stepNode<T, INSTR, FAST>(sc, tr, ins); }
+    else if (pick == 1) { if (cls == 1) stepSphere<T, S, INSTR>(sc, tr, qtime, ins); }
+    else if (pick == 2) { if (cls == 2) stepRect<T, INSTR>(sc, tr, ins); }
+    else if (pick == 3) { if (cls == 3) stepRare<T, INSTR, FAST>(sc, tr, ps.rng, ins); }
+    else {
+      // ---- shade class: (1) consume finished queries
+      bool start = false; V3<T> qo = tr.o, qd = tr.d;
+      if (cls == 4 && ps.phase != PH_IDLE) start = shadeStep<T, INSTR>(sc, tr, ps, ins, qo, qd);
+      // ---- (2) path regeneration: idle lanes take the next path indices of the warp's chunk, in lane order
+      unsigned idle = __ballot_sync(0xffffffffu, ps.phase == PH_IDLE);
+      while (idle) {
+        if (cNext >= cEnd) {
+          if (exhausted) break;
+          unsigned long long base = 0;
+          if (lane == 0) base = atomicAdd(a.counter, (unsigned long long)a.chunk);
+          base = __shfl_sync(0xffffffffu, base, 0);
+          if (base >= a.total_paths) { exhausted = true; break; }
+          cBase = cNext = base;
+          cEnd = (base + a.chunk < a.total_paths) ? base + a.chunk : a.total_paths;
+          cPix0 = (uint32_t)(base / a.ns); cS0 = (uint32_t)(base % a.ns);
+        }
+        const unsigned rank = __popc(idle & ltMask);
+        if (ps.phase == PH_IDLE && cNext + rank < cEnd) {
+          // path index -> (pixel of the region, sample); consecutive indices = consecutive samples of one pixel
+          const uint32_t off = cS0 + (uint32_t)(cNext - cBase) + rank;
+          const uint32_t pl = cPix0 + off / a.ns, s = a.s0 + off % a.ns;
+          const uint32_t row = a.row0 + pl / regionW, col = a.col0 + pl % regionW;
+          const uint32_t pixel = row * a.W + col;
+          if (pixel != ps.accPix) { flush(); ps.accPix = pixel; ps.acc0 = ps.acc1 = ps.acc2 = 0; }
+          ps.rng = streamGen(a.seed, pixel, s);
+          ins.count(0);
+          // uniformRandomUVs (Lib.hs:1362-1365): u = (x + ru)/W, v = (y + rv)/H with y counted from the bottom row
+          const T ru = rnd<T>(ps.rng), rv = rnd<T>(ps.rng);
+          const T u = ((T)col + ru) / (T)a.W, v = ((T)(a.H - 1 - row) + rv) / (T)a.H;
+          // getRay (Lib.hs:1253-1267): lens sample and shutter time are drawn for every ray
+          const V3<T> rd = scale(sc.cam[21], randomInUnitDisk<T>(ps.rng));
+          const V3<T> cu = mk<T>(sc.cam[12], sc.cam[13], sc.cam[14]), cv = mk<T>(sc.cam[15], sc.cam[16], sc.cam[17]);
+          const V3<T> offset = scale(rd.x, cu) + scale(rd.y, cv);
+          const T r = rnd<T>(ps.rng);
+          ps.time = sc.cam[22] + (sc.cam[23] - sc.cam[22]) * r;
+          const V3<T> org = mk<T>(sc.cam[0], sc.cam[1], sc.cam[2]);
+          qo = org + offset;
+          qd = mk<T>(sc.cam[3], sc.cam[4], sc.cam[5]) + scale(u, mk<T>(sc.cam[6], sc.cam[7], sc.cam[8])) + scale(v, mk<T>(sc.cam[9], sc.cam[10], sc.cam[11])) - org - offset;
+          ps.beta = mk<T>(1, 1, 1); ps.depthLeft = (int)a.maxDepth;
+          ps.phase = PH_MAIN; start = true;
+          if (ps.depthLeft <= 0) { ps.phase = PH_IDLE; start = false; }  // rayColor with depth <= 0 is black (Lib.hs:1303-1304)
+        }
+        const unsigned long long avail = cEnd - cNext; const unsigned n = __popc(idle);
+        cNext += (n < avail) ? n : avail;
+        idle = __ballot_sync(0xffffffffu, ps.phase == PH_IDLE);
+      }
+      // ---- (3) start the next query: the bounce's `hit world` (Lib.hs:1309) or one `hit htbl (Ray o v 0)` of htblPdfValue (677)
+      if (start) {
+        ins.count(13);
+        if (ps.phase == PH_MAIN) ins.count(1);
+        travBegin<T, FAST>(tr, ps.phase == PH_MAIN ? sc.world_root : ps.curLight, qo, qd, kEps<T>(), kInf<T>());
+      } else if (cls == 4) {
+        tr.cur = kEmpty;
+      }
+    }
+  }
+  flush();
+  if constexpr (INSTR == 1) {
+    for (int i = 0; i < 16; ++i) if (ins.c[i]) atomicAdd(a.ctr + i, (unsigned long long)ins.c[i]);
+  }
+}
+
+// K1: one ray per thread, the same step functions run to completion, with the visit log
+template <class T, class S, bool FAST>
+__global__ void __launch_bounds__(kBlock) traceKernel(const __grid_constant__ DScene<T> sc, const __grid_constant__ TraceArgs a) {
+  extern __shared__ uint32_t smem[];
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n) return;
+  const double* r = a.rays + (size_t)i * 7;
+  const V3<T> o = mk<T>((T)r[0], (T)r[1], (T)r[2]), d = mk<T>((T)r[3], (T)r[4], (T)r[5]);
+  const T time = (T)r[6];
+  Rng rng = streamGen(a.seed, i, 0);
+  Instr<2> ins; ins.init(a.vlog + (size_t)i * a.logStride, a.logStride);
+  for (uint32_t k = 0; k < a.logStride; ++k) a.vlog[(size_t)i * a.logStride + k] = kNone;
+  Trav<T> tr;
+  tr.col = smem + threadIdx.x; tr.stride = blockDim.x; tr.xbase = a.stackCap;
+  travBegin<T, FAST>(tr, sc.world_root, o, d, (T)a.tmin, (T)a.tmax);
+  travRun<T, S, 2, FAST>(sc, tr, time, rng, ins);
+  a.nvisit[i] = ins.n; a.vhash[i] = ins.h;
+  a.hit[i] = tr.qhit ? 1 : 0;
+  double* out = a.rec + (size_t)i * 9;
+  if (tr.qhit) {
+    HitRec<T> rec;
+    evalHit<T>(sc, o, d, time, tr.tbest, tr.bprim, tr.baux(), tr.bdepth(), &tr.x(X_BCHAIN), tr.stride, rec);
+    out[0] = rec.t; out[1] = rec.p.x; out[2] = rec.p.y; out[3] = rec.p.z; out[4] = rec.n.x; out[5] = rec.n.y; out[6] = rec.n.z; out[7] = rec.u; out[8] = rec.v;
+    a.prim[i] = tr.bprim; a.mat[i] = rec.mat; a.front[i] = rec.front ? 1 : 0;
+  } else {
+    for (int k = 0; k < 9; ++k) out[k] = 0;
+    a.prim[i] = 0; a.mat[i] = kNone; a.front[i] = 0;
+  }
+}
+

@@ -1,0 +1,236 @@
+// rt_traverse.cuh — `hit root ray t_min t_max` (Lib.hs:970-1109) as a resumable explicit-stack machine.
+//
+// The traversal state of one query lives in registers (Trav) plus a per-thread column of shared memory (stack + rarely
+// used frame / medium state), and advances by ONE step at a time:
+//     stepNode   : a BVHNode — the three independent slab tests (Lib.hs:798-814), then left child next, right child stacked
+//     stepSphere : a Sphere or MovingSphere leaf (one code path for both)
+//     stepRect   : a Rect or Cuboid leaf
+//     stepRare   : Translate / Rotate frames and their exit markers, ConstantMedium and its two boundary sub-queries,
+//                  Unhittable
+// so that the render kernel can schedule, per warp iteration, the step class most lanes are waiting for (rt_kernels.cuh).
+// Per lane the sequence of steps is exactly the reference's evaluation order:
+//  * BVHNode (971-988): left first, then right with t_max := running closest t; any later accepted hit replaces the earlier
+//    one — a DFS with a running closest t in which every accepted primitive overwrites the record.
+//  * Translate / Rotate (1029-1052) open a frame: the ray is transformed, a frame-exit marker is stacked under the child;
+//    t is frame-invariant so the running closest t carries through.  The record transform is deferred: the chain of open
+//    frames is stored with the hit and replayed once by evalHit().
+//  * ConstantMedium (1053-1080) runs two sub-queries on its boundary with their own [t_min,t_max] and only needs their t;
+//    the outer query state is parked in shared memory meanwhile (one level of nesting, validated on upload).
+#pragma once
+#include "rt_device.cuh"
+
+namespace rtb {
+
+constexpr uint32_t kEmpty = 0xffffffffu;  // Trav::cur when the query has no step left
+
+// shared-memory column layout (entry e of thread t at col[e * stride]); stack first, then the extras
+//   X_CHAIN..+3  open frames (transform refs)        X_BCHAIN..+3 frames of the best hit
+//   X_STMIN, X_STBEST, X_H1T (T, 2 words each)       X_WORLD..+11 world ray o,d (T, 2 words each) saved while frames are open
+constexpr int X_CHAIN = 0, X_BCHAIN = 4, X_STMIN = 8, X_STBEST = 10, X_H1T = 12, X_WORLD = 14, kExtraSlots = 26;
+
+// Trav::flags bit fields
+constexpr uint32_t F_INSUB = 1u, F_SQHIT = 2u;
+constexpr int F_FD_SHIFT = 4, F_BDEPTH_SHIFT = 8, F_BAUX_SHIFT = 12;
+
+template <class T> struct Trav {
+  V3<T> o, d;       // ray in the current frame
+  V3<T> inv;        // 1/d (FAST only)
+  T tmin, tbest;    // the query's t_min and its running closest t (t_max)
+  uint32_t cur;     // next hittable ref / marker to process, kEmpty when done
+  uint32_t bprim;   // primitive of the best hit (valid when qhit, outside sub-queries)
+  uint32_t flags;   // F_INSUB | F_SQHIT | fd << 4 | bdepth << 8 | baux << 12
+  int sp;           // stack entries in use
+  bool qhit;
+  uint32_t* col;    // this thread's shared-memory column
+  uint32_t stride;  // threads per block
+  uint32_t xbase;   // first extra slot = stack capacity
+
+  RTB_D void push(uint32_t v) { col[sp * stride] = v; ++sp; }
+  RTB_D void next() { if (sp > 0) { --sp; cur = col[sp * stride]; } else cur = kEmpty; }
+  RTB_D uint32_t& x(int slot) { return col[(xbase + slot) * stride]; }
+  RTB_D int fd() const { return (int)((flags >> F_FD_SHIFT) & 7u); }
+  RTB_D int bdepth() const { return (int)((flags >> F_BDEPTH_SHIFT) & 7u); }
+  RTB_D uint32_t baux() const { return (flags >> F_BAUX_SHIFT) & 7u; }
+  RTB_D void setFd(int v) { flags = (flags & ~(7u << F_FD_SHIFT)) | ((uint32_t)v << F_FD_SHIFT); }
+};
+
+RTB_D void stT(uint32_t* p, uint32_t stride, float v) { p[0] = __float_as_uint(v); }
+RTB_D void stT(uint32_t* p, uint32_t stride, double v) { unsigned long long b = (unsigned long long)__double_as_longlong(v); p[0] = (uint32_t)b; p[stride] = (uint32_t)(b >> 32); }
+RTB_D void ldT(const uint32_t* p, uint32_t stride, float& v) { v = __uint_as_float(p[0]); }
+RTB_D void ldT(const uint32_t* p, uint32_t stride, double& v) { v = __longlong_as_double((long long)((unsigned long long)p[0] | ((unsigned long long)p[stride] << 32))); }
+
+template <class T, bool FAST> RTB_D void setInv(Trav<T>& tr) {
+  if (FAST) tr.inv = mk<T>((T)1 / tr.d.x, (T)1 / tr.d.y, (T)1 / tr.d.z);
+}
+
+// start `hit root (Ray o d _) t_min t_max`
+template <class T, bool FAST>
+RTB_D void travBegin(Trav<T>& tr, uint32_t root, const V3<T>& o, const V3<T>& d, T t_min, T t_max) {
+  tr.o = o; tr.d = d; setInv<T, FAST>(tr);
+  tr.tmin = t_min; tr.tbest = t_max; tr.cur = root; tr.bprim = 0; tr.flags = 0; tr.sp = 0; tr.qhit = false;
+}
+
+// an accepted primitive hit replaces the record (Lib.hs:979-987)
+template <class T> RTB_D void travAccept(Trav<T>& tr, T t, uint32_t ref, uint32_t aux) {
+  tr.tbest = t; tr.qhit = true;
+  if (!(tr.flags & F_INSUB)) {
+    const int fd = tr.fd();
+    tr.bprim = ref;
+    tr.flags = (tr.flags & 0xffu) | ((uint32_t)fd << F_BDEPTH_SHIFT) | (aux << F_BAUX_SHIFT);
+    for (int i = 0; i < fd; ++i) tr.x(X_BCHAIN + i) = tr.x(X_CHAIN + i);
+  }
+}
+
+template <class T, int INSTR, bool FAST>
+RTB_D void stepNode(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
+  const uint32_t idx = tr.cur & 0x0fffffffu;
+  ins.visit(tr.cur); ins.boxTest();
+  const Q4<T> lo = ldq(sc.nodes + 2 * (size_t)idx), hi = ldq(sc.nodes + 2 * (size_t)idx + 1);
+  const bool bx = slab<T, FAST>(lo.x, hi.x, tr.o.x, tr.d.x, tr.inv.x, tr.tmin, tr.tbest);
+  const bool by = slab<T, FAST>(lo.y, hi.y, tr.o.y, tr.d.y, tr.inv.y, tr.tmin, tr.tbest);
+  const bool bz = slab<T, FAST>(lo.z, hi.z, tr.o.z, tr.d.z, tr.inv.z, tr.tmin, tr.tbest);
+  if (bx && by && bz) { tr.push(bitsOf(hi.w)); tr.cur = bitsOf(lo.w); }
+  else tr.next();
+}
+
+template <class T, class S, int INSTR>
+RTB_D void stepSphere(const DScene<T>& sc, Trav<T>& tr, T time, Instr<INSTR>& ins) {
+  const uint32_t ref = tr.cur, idx = ref & 0x0fffffffu;
+  ins.visit(ref);
+  V3<T> ctr; T rad;
+  if ((ref >> 28) == K_SPHERE) {
+    const Q4<T> q = ldq(sc.spheres + idx);
+    ctr = mk<T>(q.x, q.y, q.z); rad = q.w;
+  } else {  // MovingSphere (Lib.hs:1106-1108)
+    const Q4<T> a = ldq(sc.moving + 3 * (size_t)idx), b = ldq(sc.moving + 3 * (size_t)idx + 1), c = ldq(sc.moving + 3 * (size_t)idx + 2);
+    const V3<T> c0 = mk<T>(a.x, a.y, a.z), c1 = mk<T>(b.x, b.y, b.z);
+    ctr = c0 + scale((time - b.w) / c.x, c1 - c0); rad = a.w;
+  }
+  T t;
+  if (sphereT<T, S>(ctr, rad, tr.o, tr.d, tr.tmin, tr.tbest, t)) { ins.sphereHit(); travAccept<T>(tr, t, ref, 0); }
+  tr.next();
+}
+
+// restore the current-frame ray after a frame exit: depth 0 = the saved world ray, else replay the open chain
+template <class T, bool FAST> RTB_D void travReframe(const DScene<T>& sc, Trav<T>& tr) {
+  const int fd = tr.fd();
+  const int w = sizeof(T) / 4;
+  T v[6];
+  for (int i = 0; i < 6; ++i) ldT(&tr.x(X_WORLD + i * w), tr.stride, v[i]);
+  tr.o = mk<T>(v[0], v[1], v[2]); tr.d = mk<T>(v[3], v[4], v[5]);
+  for (int i = 0; i < fd; ++i) applyXform<T>(sc, tr.x(X_CHAIN + i), tr.o, tr.d);
+  setInv<T, FAST>(tr);
+}
+
+// Rect and Cuboid leaves
+template <class T, int INSTR>
+RTB_D void stepRect(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
+  const uint32_t ref = tr.cur, kind = ref >> 28, idx = ref & 0x0fffffffu;
+  if (kind != K_CUBOID) {
+    ins.visit(ref);
+    const Q4<T> a = ldq(sc.rects + 2 * (size_t)idx), b = ldq(sc.rects + 2 * (size_t)idx + 1);
+    T t;
+    if (rectT<T>(kind - K_RECT_XY, a.x, a.y, a.z, a.w, b.x, tr.o, tr.d, tr.tmin, tr.tbest, t)) travAccept<T>(tr, t, ref, 0);
+    tr.next();
+  } else if (kind == K_CUBOID) {  // Lib.hs:989-1004: foldr over the six rects => last first; strict `<` replaces
+    ins.visit(ref);
+    const Q4<T> mn = ldq(sc.cuboids + 2 * (size_t)idx), mx = ldq(sc.cuboids + 2 * (size_t)idx + 1);
+    bool acc = false; T tNew = 0; uint32_t aux = 0;
+#pragma unroll
+    for (int f = 5; f >= 0; --f) {
+      uint32_t plane; T i0, i1, j0, j1, k, t1;
+      cuboidFace<T>(f, mn, mx, plane, i0, i1, j0, j1, k);
+      if (rectT<T>(plane, i0, i1, j0, j1, k, tr.o, tr.d, tr.tmin, tr.tbest, t1)) {
+        if (!acc) { acc = true; tNew = t1; aux = (uint32_t)f; }
+        else if (t1 < tNew) { tNew = t1; aux = (uint32_t)f; }
+      }
+    }
+    if (acc) travAccept<T>(tr, tNew, ref, aux);
+    tr.next();
+  }
+}
+
+// the rare kinds: frames, markers, media, Unhittable (kept out of line: the hot loop stays small)
+template <class T, int INSTR, bool FAST>
+__device__ __noinline__ void stepRare(const DScene<T>& sc, Trav<T>& tr, Rng& rng, Instr<INSTR>& ins) {
+  const uint32_t ref = tr.cur, kind = ref >> 28, idx = ref & 0x0fffffffu;
+  const int w = sizeof(T) / 4;
+  if (kind == K_TRANSLATE || kind == K_ROTATE) {
+    ins.visit(ref);
+    const uint32_t child = (kind == K_TRANSLATE) ? bitsOf(ldq(sc.translates + idx).w) : bitsOf(ldq(sc.rotates + idx).w);
+    const int fd = tr.fd();
+    if (fd == 0) {  // park the world ray: restoring it must be exact, not (o - off) + off
+      const T v[6] = {tr.o.x, tr.o.y, tr.o.z, tr.d.x, tr.d.y, tr.d.z};
+      for (int i = 0; i < 6; ++i) stT(&tr.x(X_WORLD + i * w), tr.stride, v[i]);
+    }
+    tr.x(X_CHAIN + fd) = ref;
+    tr.setFd(fd + 1);
+    applyXform<T>(sc, ref, tr.o, tr.d);
+    setInv<T, FAST>(tr);
+    tr.push(K_MARK_FRAME << 28);
+    tr.cur = child;
+  } else if (kind == K_MARK_FRAME) {
+    tr.setFd(tr.fd() - 1);
+    travReframe<T, FAST>(sc, tr);
+    tr.next();
+  } else if (kind == K_MEDIUM) {  // Lib.hs:1054: hit boundary ray (-inf) inf
+    ins.visit(ref);
+    stT(&tr.x(X_STMIN), tr.stride, tr.tmin); stT(&tr.x(X_STBEST), tr.stride, tr.tbest);
+    tr.flags = (tr.flags & ~F_SQHIT) | F_INSUB | (tr.qhit ? F_SQHIT : 0u);
+    tr.tmin = -kInf<T>(); tr.tbest = kInf<T>(); tr.qhit = false;
+    tr.push((K_MARK_MED1 << 28) | idx);
+    tr.cur = bitsOf(ldq(sc.media + idx).z);
+  } else if (kind == K_MARK_MED1) {
+    if (!tr.qhit) {
+      ldT(&tr.x(X_STMIN), tr.stride, tr.tmin); ldT(&tr.x(X_STBEST), tr.stride, tr.tbest);
+      tr.qhit = (tr.flags & F_SQHIT) != 0; tr.flags &= ~F_INSUB;
+      tr.next();
+    } else {  // Lib.hs:1057: hit boundary ray (h1t + epsilon) inf
+      stT(&tr.x(X_H1T), tr.stride, tr.tbest);
+      tr.tmin = tr.tbest + kEps<T>(); tr.tbest = kInf<T>(); tr.qhit = false;
+      tr.push((K_MARK_MED2 << 28) | idx);
+      tr.cur = bitsOf(ldq(sc.media + idx).z);
+    }
+  } else if (kind == K_MARK_MED2) {
+    const bool h2 = tr.qhit; const T h2t = tr.tbest;
+    ldT(&tr.x(X_STMIN), tr.stride, tr.tmin); ldT(&tr.x(X_STBEST), tr.stride, tr.tbest);
+    tr.qhit = (tr.flags & F_SQHIT) != 0; tr.flags &= ~F_INSUB;
+    if (h2) {  // Lib.hs:1060-1079
+      T h1t; ldT(&tr.x(X_H1T), tr.stride, h1t);
+      const T rec1t_ = hmax(tr.tmin, h1t);
+      const T rec2t = hmin(tr.tbest, h2t);
+      if (!(rec1t_ >= rec2t)) {
+        const T rec1t = (rec1t_ < 0) ? (T)0 : rec1t_;
+        const T rayLength = len(tr.d);
+        const T distInside = (rec2t - rec1t) * rayLength;
+        const T xi = rnd<T>(rng);
+        const T hitDist = ldq(sc.media + idx).x * mlog(xi);
+        if (!(hitDist > distInside)) travAccept<T>(tr, rec1t + (hitDist / rayLength), (K_MEDIUM << 28) | idx, 0);
+      }
+    }
+    tr.next();
+  } else {  // Unhittable (Lib.hs:1109)
+    ins.visit(ref);
+    tr.next();
+  }
+}
+
+// step class of a lane's pending work: 0 node, 1 sphere-like leaf, 2 rect / cuboid leaf, 3 rare
+RTB_D int stepClass(uint32_t cur) {
+  const uint32_t k = cur >> 28;
+  return k == K_BVH ? 0 : ((k == K_SPHERE || k == K_MOVING) ? 1 : ((k >= K_RECT_XY && k <= K_CUBOID) ? 2 : 3));
+}
+
+// run a whole query to completion (K1 and the texture-free probes): same steps, no scheduling
+template <class T, class S, int INSTR, bool FAST>
+RTB_D void travRun(const DScene<T>& sc, Trav<T>& tr, T time, Rng& rng, Instr<INSTR>& ins) {
+  while (tr.cur != kEmpty) {
+    const int c = stepClass(tr.cur);
+    if (c == 0) stepNode<T, INSTR, FAST>(sc, tr, ins);
+    else if (c == 1) stepSphere<T, S, INSTR>(sc, tr, time, ins);
+    else if (c == 2) stepRect<T, INSTR>(sc, tr, ins);
+    else stepRare<T, INSTR, FAST>(sc, tr, rng, ins);
+  }
+}
+
+}  // namespace rtb

@@ -6,6 +6,7 @@
 #include "rt_device.cuh"
 #include "rt_launch.h"
 
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -250,6 +251,12 @@ int normaliseParams(const RtRenderParams* p, RtRenderParams& q) {
   return RT_OK;
 }
 
+// scheduler knobs of renderKernel; environment overrides are for tuning experiments only
+uint32_t tuneParam(const char* name, uint32_t dflt) {
+  const char* v = std::getenv(name);
+  return v ? (uint32_t)std::strtoul(v, nullptr, 10) : dflt;
+}
+
 // launches the render kernel into d_out (accumulating); counters optional
 int renderLaunch(SceneEntry* e, const RtRenderParams& q, double* d_out, cudaStream_t st, bool counted, int* gridOut) {
   const void* dsc = nullptr;
@@ -268,6 +275,7 @@ int renderLaunch(SceneEntry* e, const RtRenderParams& q, double* d_out, cudaStre
   unsigned long long chunk = 1024;
   while (chunk > 64 && a.total_paths / chunk < warps * 8ull) chunk /= 2;
   a.chunk = (uint32_t)chunk;
+  a.shadeMin = tuneParam("RTB_SHADE_MIN", 8); a.keepNode = tuneParam("RTB_KEEP_NODE", 16); a.keepLeaf = tuneParam("RTB_KEEP_LEAF", 16);
   a.counter = e->d_counter; a.ctr = counted ? e->d_counter + 1 : nullptr; a.out = d_out;
   cudaError_t ce = (q.flags & RT_FLAG_FAST_MATH) ? launchRender<true>((int)q.precision, counted ? 1 : 0, dsc, a, e->hs.stackDepth, e->numSMs, st, gridOut)
                                                  : launchRender<false>((int)q.precision, counted ? 1 : 0, dsc, a, e->hs.stackDepth, e->numSMs, st, gridOut);

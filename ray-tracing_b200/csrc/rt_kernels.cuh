@@ -35,7 +35,7 @@ __global__ void textureKernel(const __grid_constant__ DScene<T> sc, uint32_t tex
 template <class T, class S, int INSTR, bool FAST>
 static cudaError_t launchRenderT(const DScene<T>& sc, const RenderArgs& a, int stackDepth, int numSMs, cudaStream_t st, int* gridOut) {
   auto kern = renderKernel<T, S, INSTR, FAST>;
-  size_t smem = (size_t)(stackDepth + kExtraSlots) * kBlock * sizeof(uint32_t);
+  size_t smem = (size_t)(stackDepth + extraWords<T>()) * kBlock * sizeof(uint32_t) + (kBlock / 32) * 16;  // columns + per-warp chunk slots
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   int perSM = 0;
@@ -66,7 +66,7 @@ cudaError_t launchRender(int prec, int instr, const void* dscene, const RenderAr
 template <class T, class S, bool FAST>
 static cudaError_t launchTraceT(const DScene<T>& sc, const TraceArgs& a, int stackDepth, cudaStream_t st) {
   auto kern = traceKernel<T, S, FAST>;
-  size_t smem = (size_t)(stackDepth + kExtraSlots) * kBlock * sizeof(uint32_t);
+  size_t smem = (size_t)(stackDepth + extraWords<T>()) * kBlock * sizeof(uint32_t);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   TraceArgs b = a; b.stackCap = (uint32_t)stackDepth;

@@ -12,6 +12,8 @@ struct RenderArgs {
   uint32_t row0, row1, col0, col1; // region (rows counted from the top)
   uint32_t chunk;                  // path indices a warp takes per atomic
   uint32_t stackCap;               // traversal stack entries per thread (set by the launcher)
+  uint32_t shadeMin;               // run the shade class as soon as this many lanes wait for it
+  uint32_t keepNode, keepLeaf;     // stay in the node / sphere inner loop while more than live * keep / 32 lanes remain in the class
   unsigned long long seed;
   unsigned long long total_paths;  // region pixels * ns
   unsigned long long* counter;     // device: next free path index

@@ -3,40 +3,56 @@
 // renderKernel: persistent warps, one camera path per lane.  Every lane is a small state machine whose pending work falls in
 // one of five classes: a BVH-node step, a sphere-leaf step, a rect/cuboid-leaf step, a rare traversal step, or "shade"
 // (consume a finished query: build the hit record, scatter, start the next query, or end the path and take the next path
-// index of the warp's chunk).  Each warp iteration ballots the classes and runs the ONE class most lanes are waiting for
-// (with ageing so no lane starves): divergent paths are regrouped by what they need to do next instead of executing every
-// branch with a handful of lanes.  Per lane the order of steps, and of RNG draws, is unchanged — results do not depend on
-// the schedule.
+// index of the warp's chunk).  Each warp iteration ballots the classes and runs the class MOST lanes are waiting for; lanes of
+// the other classes wait and accumulate, so divergent paths are regrouped by what they need to do next instead of executing
+// every branch with a handful of lanes.  The node and sphere classes then stay in a tight inner loop (one ballot per step)
+// for as long as enough lanes remain in the class.  Per lane the order of steps, and of RNG draws, is unchanged — results do
+// not depend on the schedule.
+//
+// Register discipline: the hot state (ray, t-interval, cursor, stack pointer, throughput, RNG) is scalars in registers; all
+// rarely touched state (frame chains, parked medium query, light-pdf walk, per-pixel accumulator) lives in the thread's
+// shared-memory column (rt_traverse.cuh) so the hot loop neither spills nor drags cold registers along.
 
 enum : int { PH_IDLE = 0, PH_MAIN = 1, PH_LPDF = 2 };
-constexpr int kShadeMin = 8;    // run the shade class as soon as this many lanes wait for it
-constexpr int kAgeShade = 24;   // ... or when it has waited this many iterations
-constexpr int kAgeTrav = 6;     // a non-empty traversal class is run at the latest after this many iterations
 
 template <class T> struct PathState {
   V3<T> beta; T time; int depthLeft; int phase; Rng rng;
-  double acc0, acc1, acc2; uint32_t accPix;
-  T l_spdf, l_v2, l_v1, curW; uint32_t curLight; int lsp;
-  uint32_t lref[kMaxLightDepth]; T lwt[kMaxLightDepth];
 };
 
-// consume the finished query of this lane.  Returns true when a new query must be started on ray (qo, qd) with root qroot.
+RTB_D double ldD(const uint32_t* p, uint32_t stride) { return __longlong_as_double((long long)((unsigned long long)p[0] | ((unsigned long long)p[stride] << 32))); }
+RTB_D void stD(uint32_t* p, uint32_t stride, double v) { unsigned long long b = (unsigned long long)__double_as_longlong(v); p[0] = (uint32_t)b; p[stride] = (uint32_t)(b >> 32); }
+
+// add a finished path's radiance to the lane's accumulator (current pixel)
+template <class T> RTB_D void accAdd(Trav<T>& tr, const V3<T>& L) {
+  stD(&tr.xw(XW_ACC + 0), tr.stride, ldD(&tr.xw(XW_ACC + 0), tr.stride) + (double)L.x);
+  stD(&tr.xw(XW_ACC + 2), tr.stride, ldD(&tr.xw(XW_ACC + 2), tr.stride) + (double)L.y);
+  stD(&tr.xw(XW_ACC + 4), tr.stride, ldD(&tr.xw(XW_ACC + 4), tr.stride) + (double)L.z);
+}
+template <class T> RTB_D void accFlush(Trav<T>& tr, double* out) {
+  const uint32_t pix = tr.xw(XW_ACCPIX);
+  if (pix != kNone) {
+    atomicAdd(out + (size_t)pix * 3, ldD(&tr.xw(XW_ACC + 0), tr.stride));
+    atomicAdd(out + (size_t)pix * 3 + 1, ldD(&tr.xw(XW_ACC + 2), tr.stride));
+    atomicAdd(out + (size_t)pix * 3 + 2, ldD(&tr.xw(XW_ACC + 4), tr.stride));
+  }
+}
+
+// consume the finished query of this lane.  Returns true when a new query must be started on ray (qo, qd); its root is
+// world_root in phase PH_MAIN and the light in slot X_CURLIGHT in phase PH_LPDF.
 template <class T, int INSTR>
 __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, PathState<T>& ps, Instr<INSTR>& ins, V3<T>& qo, V3<T>& qd) {
-  const uint32_t lightsKind = sc.lights_root >> 28;
-  auto finish = [&](const V3<T>& L) { ps.acc0 += (double)L.x; ps.acc1 += (double)L.y; ps.acc2 += (double)L.z; ps.phase = PH_IDLE; };
   bool scattered = false;  // the path continues with (qo, qd) as the next bounce ray
   qo = tr.o; qd = tr.d;    // all frames are closed when a query ends: this is the query's world ray
   if (ps.phase == PH_MAIN) {
-    if (!tr.qhit) { finish(ps.beta * mk<T>(sc.bg[0], sc.bg[1], sc.bg[2])); return false; }  // Lib.hs:1310-1313
+    if (!tr.qhit()) { accAdd<T>(tr, ps.beta * mk<T>(sc.bg[0], sc.bg[1], sc.bg[2])); ps.phase = PH_IDLE; return false; }  // Lib.hs:1310-1313
     HitRec<T> rec;
-    evalHit<T>(sc, tr.o, tr.d, ps.time, tr.tbest, tr.bprim, tr.baux(), tr.bdepth(), &tr.x(X_BCHAIN), tr.stride, rec);
+    evalHit<T>(sc, tr.o, tr.d, ps.time, tr.tbest, tr.bprim, tr.baux(), tr.bdepth(), &tr.xu(X_BCHAIN), tr.stride * (uint32_t)(sizeof(T) / 4), rec);
     const Q4<T> m = ldq(sc.mats + rec.mat);
     const uint32_t mkind = bitsOf(m.x), tex = bitsOf(m.y);
     if (mkind == M_LIGHT) {  // scatter = Nothing -> emitted, back face only (Lib.hs:860, 880-885)
       V3<T> e = mk<T>(0, 0, 0);
       if (!rec.front) e = textureValue<T, INSTR>(sc, tex, rec.u, rec.v, rec.p, ins);
-      finish(ps.beta * e);
+      accAdd<T>(tr, ps.beta * e); ps.phase = PH_IDLE;
       return false;
     } else if (mkind == M_LAMBERTIAN) {  // Lib.hs:823-836 with pdfGenerate/pdfValue of the mixture (367-382)
       const V3<T> att = textureValue<T, INSTR>(sc, tex, rec.u, rec.v, rec.p, ins);
@@ -47,18 +63,20 @@ __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, Path
       else pdfD = onbLocal(uvw, randomCosineDirection<T>(ps.rng));
       const V3<T> dir = unit(pdfD);
       const T cosine = dot(unit(dir), uvw.w);
-      ps.l_v2 = (cosine <= 0) ? (T)0 : cosine / kPi<T>();
+      const T v2 = (cosine <= 0) ? (T)0 : cosine / kPi<T>();
       const T c2 = dot(rec.n, dir);  // scatteringPdf (Lib.hs:874-878)
-      ps.l_spdf = (c2 < 0) ? (T)0 : c2 / kPi<T>();
+      const T spdf = (c2 < 0) ? (T)0 : c2 / kPi<T>();
       ps.beta = ps.beta * att;
       qo = rec.p; qd = dir;
-      if (lightsKind == K_UNHITTABLE) {  // htblPdfValue Unhittable = 0 without any traversal (Lib.hs:677-680, 1109)
+      if ((sc.lights_root >> 28) == K_UNHITTABLE) {  // htblPdfValue Unhittable = 0 without any traversal (Lib.hs:677-680, 1109)
         ins.count(13); ins.visit(sc.lights_root);
-        const T pdfVal = (T)0.5 * ((T)0 + ps.l_v2);
-        ps.beta = scale(ps.l_spdf / pdfVal, ps.beta);
+        const T pdfVal = (T)0.5 * ((T)0 + v2);
+        ps.beta = scale(spdf / pdfVal, ps.beta);
         scattered = true;
       } else {
-        ps.phase = PH_LPDF; ps.l_v1 = 0; ps.lsp = 0; ps.curLight = sc.lights_root; ps.curW = 1;
+        ps.phase = PH_LPDF;
+        xst<T>(tr, X_LV2, v2); xst<T>(tr, X_LSPDF, spdf); xst<T>(tr, X_LV1, (T)0); xst<T>(tr, X_CURW, (T)1);
+        tr.xu(X_LSP) = 0; tr.xu(X_CURLIGHT) = sc.lights_root;
         return true;
       }
     } else if (mkind == M_METAL) {  // Lib.hs:837-841: never absorbs, fuzz unclamped
@@ -86,37 +104,44 @@ __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, Path
       qo = rec.p; qd = randDr;
       scattered = true;
     }
-  } else {  // PH_LPDF: htblPdfValue (Lib.hs:673-705) for `curLight`, walked depth-first, left first
-    if (tr.qhit) {
-      const uint32_t lk = ps.curLight >> 28, li = ps.curLight & 0x0fffffffu;
+  } else {  // PH_LPDF: htblPdfValue (Lib.hs:673-705) for the light in X_CURLIGHT, walked depth-first, left first
+    const uint32_t curLight = tr.xu(X_CURLIGHT);
+    const T curW = xld<T>(tr, X_CURW);
+    uint32_t lsp = tr.xu(X_LSP);
+    if (tr.qhit()) {
+      const uint32_t lk = curLight >> 28, li = curLight & 0x0fffffffu;
       if (lk == K_RECT_XZ) {
         const Q4<T> ra = ldq(sc.rects + 2 * (size_t)li);
         const T area = (ra.y - ra.x) * (ra.w - ra.z);
         const T distanceSquared = tr.tbest * tr.tbest * sqlen(tr.d);
         const T cosine = mabs(tr.d.y / len(tr.d));  // |v . (0,+-1,0)| / |v|
-        ps.l_v1 = ps.l_v1 + ps.curW * (distanceSquared / (cosine * area));
+        xst<T>(tr, X_LV1, xld<T>(tr, X_LV1) + curW * (distanceSquared / (cosine * area)));
       } else if (lk == K_SPHERE) {
         const Q4<T> q = ldq(sc.spheres + li);
         const T cosThetaMax = msqrt(1 - q.w * q.w / sqlen(mk<T>(q.x, q.y, q.z) - tr.o));
         const T solidAngle = 2 * kPi<T>() * (1 - cosThetaMax);
-        ps.l_v1 = ps.l_v1 + ps.curW * (1 / solidAngle);
+        xst<T>(tr, X_LV1, xld<T>(tr, X_LV1) + curW * (1 / solidAngle));
       } else if (lk == K_BVH) {
         const uint4 sz = __ldg(sc.node_sz + li);
         const uint32_t lc = bitsOf(ldq(sc.nodes + 2 * (size_t)li).w), rc = bitsOf(ldq(sc.nodes + 2 * (size_t)li + 1).w);
-        if (ps.lsp + 2 <= kMaxLightDepth) {
-          ps.lref[ps.lsp] = rc; ps.lwt[ps.lsp] = ps.curW * ((T)sz.z / (T)sz.x); ++ps.lsp;
-          ps.lref[ps.lsp] = lc; ps.lwt[ps.lsp] = ps.curW * ((T)sz.y / (T)sz.x); ++ps.lsp;
+        if (lsp + 2 <= (uint32_t)kMaxLightDepth) {
+          tr.xu(X_LREF + (int)lsp) = rc; xst<T>(tr, X_LWT + (int)lsp, curW * ((T)sz.z / (T)sz.x)); ++lsp;
+          tr.xu(X_LREF + (int)lsp) = lc; xst<T>(tr, X_LWT + (int)lsp, curW * ((T)sz.y / (T)sz.x)); ++lsp;
         }
       }
     }
-    if (ps.lsp > 0) { --ps.lsp; ps.curLight = ps.lref[ps.lsp]; ps.curW = ps.lwt[ps.lsp]; return true; }
-    const T pdfVal = (T)0.5 * (ps.l_v1 + ps.l_v2);
-    ps.beta = scale(ps.l_spdf / pdfVal, ps.beta);
+    if (lsp > 0) {
+      --lsp;
+      tr.xu(X_CURLIGHT) = tr.xu(X_LREF + (int)lsp); xst<T>(tr, X_CURW, xld<T>(tr, X_LWT + (int)lsp)); tr.xu(X_LSP) = lsp;
+      return true;
+    }
+    const T pdfVal = (T)0.5 * (xld<T>(tr, X_LV1) + xld<T>(tr, X_LV2));
+    ps.beta = scale(xld<T>(tr, X_LSPDF) / pdfVal, ps.beta);
     ps.phase = PH_MAIN; scattered = true;
   }
   if (scattered) {  // rayColorHelp newRay (d - 1) (Lib.hs:1321-1333)
     --ps.depthLeft;
-    if (ps.depthLeft <= 0) { finish(ps.beta * mk<T>(0, 0, 0)); return false; }
+    if (ps.depthLeft <= 0) { accAdd<T>(tr, ps.beta * mk<T>(0, 0, 0)); ps.phase = PH_IDLE; return false; }
     return true;
   }
   return false;
@@ -132,75 +157,84 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
 
   Trav<T> tr;
   tr.col = smem + threadIdx.x; tr.stride = blockDim.x; tr.xbase = a.stackCap;
-  tr.cur = kEmpty; tr.sp = 0; tr.qhit = false; tr.flags = 0; tr.bprim = 0; tr.tmin = 0; tr.tbest = 0;
+  tr.cur = kEmpty; tr.sp = 0; tr.flags = 0; tr.bprim = 0; tr.tmin = 0; tr.tbest = 0;
   tr.o = mk<T>(0, 0, 0); tr.d = mk<T>(0, 0, 1); tr.inv = mk<T>(0, 0, 0);
   PathState<T> ps;
   ps.phase = PH_IDLE; ps.beta = mk<T>(1, 1, 1); ps.time = 0; ps.depthLeft = 0; ps.rng = Rng{0, 1};
-  ps.acc0 = ps.acc1 = ps.acc2 = 0; ps.accPix = kNone;
-  ps.l_spdf = ps.l_v2 = ps.l_v1 = 0; ps.curW = 1; ps.curLight = 0; ps.lsp = 0;
-  unsigned long long cNext = 0, cEnd = 0, cBase = 0; uint32_t cPix0 = 0, cS0 = 0; bool exhausted = false;
+  tr.xw(XW_ACCPIX) = kNone;
+  // the warp's chunk of the path index space: {first pixel of the region, first sample, next offset, end offset}
+  volatile uint32_t* ws = smem + (size_t)(a.stackCap + extraWords<T>()) * blockDim.x + (threadIdx.x >> 5) * 4;
+  if (lane == 0) { ws[0] = 0; ws[1] = 0; ws[2] = 0; ws[3] = 0; }
+  __syncwarp();
+  bool exhausted = false;
   const uint32_t regionW = a.col1 - a.col0;
-  int age0 = 0, age1 = 0, age2 = 0, age3 = 0, age4 = 0;
-
-  auto flush = [&]() {
-    if (ps.accPix != kNone) {
-      atomicAdd(a.out + (size_t)ps.accPix * 3, ps.acc0); atomicAdd(a.out + (size_t)ps.accPix * 3 + 1, ps.acc1); atomicAdd(a.out + (size_t)ps.accPix * 3 + 2, ps.acc2);
-    }
-  };
 
   for (;;) {
     // ---- classify this lane's pending work and vote
-    const bool dead = (ps.phase == PH_IDLE) && exhausted;
-    const int cls = dead ? -1 : (tr.cur == kEmpty ? 4 : stepClass(tr.cur));
+    const int cls = stepClass(tr.cur);
     const unsigned m0 = __ballot_sync(0xffffffffu, cls == 0), m1 = __ballot_sync(0xffffffffu, cls == 1), m2 = __ballot_sync(0xffffffffu, cls == 2),
                    m3 = __ballot_sync(0xffffffffu, cls == 3), m4 = __ballot_sync(0xffffffffu, cls == 4);
-    if ((m0 | m1 | m2 | m3 | m4) == 0u) break;
+    const unsigned live = m0 | m1 | m2 | m3 | m4;
+    if (live == 0u) break;
     const int c0 = __popc(m0), c1 = __popc(m1), c2 = __popc(m2), c3 = __popc(m3), c4 = __popc(m4);
-    int pick;
-    if ((c0 + c1 + c2 + c3) == 0 || c4 >= kShadeMin || (c4 > 0 && age4 >= kAgeShade)) pick = 4;
-    else if (c3 > 0 && age3 >= kAgeTrav) pick = 3;
-    else if (c2 > 0 && age2 >= kAgeTrav) pick = 2;
-    else if (c1 > 0 && age1 >= kAgeTrav) pick = 1;
-    else if (c0 > 0 && age0 >= kAgeTrav) pick = 0;
-    else {
-      pick = 0; int best = c0;
-      if (c1 > best) { pick = 1; best = c1; }
-      if (c2 > best) { pick = 2; best = c2; }
-      if (c3 > best) { pick = 3; best = c3; }
-    }
-    age0 = (c0 > 0 && pick != 0) ? age0 + 1 : 0; age1 = (c1 > 0 && pick != 1) ? age1 + 1 : 0; age2 = (c2 > 0 && pick != 2) ? age2 + 1 : 0;
-    age3 = (c3 > 0 && pick != 3) ? age3 + 1 : 0; age4 = (c4 > 0 && pick != 4) ? age4 + 1 : 0;
+    int pick = 0, best = c0;
+    if (c1 > best) { pick = 1; best = c1; }
+    if (c2 > best) { pick = 2; best = c2; }
+    if (c3 > best) { pick = 3; best = c3; }
+    if (c4 > best || c4 >= (int)a.shadeMin) pick = 4;
 
-    const T qtime = (ps.phase == PH_MAIN) ? ps.time : (T)0;  // htblPdfValue traces with time 0 (Lib.hs:677)
-    if (pick == 0) { if (cls == 0) stepNode<T, INSTR, FAST>(sc, tr, ins); }
-    else if (pick == 1) { if (cls == 1) stepSphere<T, S, INSTR>(sc, tr, qtime, ins); }
-    else if (pick == 2) { if (cls == 2) stepRect<T, INSTR>(sc, tr, ins); }
-    else if (pick == 3) { if (cls == 3) stepRare<T, INSTR, FAST>(sc, tr, ps.rng, ins); }
-    else {
+    if (pick == 0) {  // stay on node steps while enough lanes remain in the class
+      const int keep = (__popc(live) * (int)a.keepNode) >> 5;
+      int n;
+      do {
+        if ((tr.cur >> 28) == K_BVH) stepNode<T, INSTR, FAST>(sc, tr, ins);
+        n = __popc(__ballot_sync(0xffffffffu, (tr.cur >> 28) == K_BVH));
+      } while (n > keep);
+    } else if (pick == 1) {
+      const T qtime = (ps.phase == PH_MAIN) ? ps.time : (T)0;  // htblPdfValue traces with time 0 (Lib.hs:677)
+      const int keep = (__popc(live) * (int)a.keepLeaf) >> 5;
+      int n;
+      do {
+        const uint32_t k = tr.cur >> 28;
+        if (k == K_SPHERE || k == K_MOVING) stepSphere<T, S, INSTR>(sc, tr, qtime, ins);
+        const uint32_t k2 = tr.cur >> 28;
+        n = __popc(__ballot_sync(0xffffffffu, k2 == K_SPHERE || k2 == K_MOVING));
+      } while (n > keep);
+    } else if (pick == 2) {
+      if (cls == 2) stepRect<T, INSTR>(sc, tr, ins);
+    } else if (pick == 3) {
+      if (cls == 3) stepRare<T, INSTR, FAST>(sc, tr, ps.rng, ins);
+    } else {
       // ---- shade class: (1) consume finished queries
       bool start = false; V3<T> qo = tr.o, qd = tr.d;
       if (cls == 4 && ps.phase != PH_IDLE) start = shadeStep<T, INSTR>(sc, tr, ps, ins, qo, qd);
       // ---- (2) path regeneration: idle lanes take the next path indices of the warp's chunk, in lane order
-      unsigned idle = __ballot_sync(0xffffffffu, ps.phase == PH_IDLE);
+      unsigned idle = __ballot_sync(0xffffffffu, cls == 4 && ps.phase == PH_IDLE);
       while (idle) {
+        uint32_t cNext = ws[2], cEnd = ws[3];
         if (cNext >= cEnd) {
           if (exhausted) break;
           unsigned long long base = 0;
           if (lane == 0) base = atomicAdd(a.counter, (unsigned long long)a.chunk);
           base = __shfl_sync(0xffffffffu, base, 0);
           if (base >= a.total_paths) { exhausted = true; break; }
-          cBase = cNext = base;
-          cEnd = (base + a.chunk < a.total_paths) ? base + a.chunk : a.total_paths;
-          cPix0 = (uint32_t)(base / a.ns); cS0 = (uint32_t)(base % a.ns);
+          cNext = 0;
+          cEnd = (base + a.chunk < a.total_paths) ? a.chunk : (uint32_t)(a.total_paths - base);
+          if (lane == 0) { ws[0] = (uint32_t)(base / a.ns); ws[1] = (uint32_t)(base % a.ns); ws[3] = cEnd; }
+          __syncwarp();
         }
         const unsigned rank = __popc(idle & ltMask);
-        if (ps.phase == PH_IDLE && cNext + rank < cEnd) {
+        if (cls == 4 && ps.phase == PH_IDLE && cNext + rank < cEnd) {
           // path index -> (pixel of the region, sample); consecutive indices = consecutive samples of one pixel
-          const uint32_t off = cS0 + (uint32_t)(cNext - cBase) + rank;
-          const uint32_t pl = cPix0 + off / a.ns, s = a.s0 + off % a.ns;
+          const uint32_t off = ws[1] + cNext + rank;
+          const uint32_t pl = ws[0] + off / a.ns, s = a.s0 + off % a.ns;
           const uint32_t row = a.row0 + pl / regionW, col = a.col0 + pl % regionW;
           const uint32_t pixel = row * a.W + col;
-          if (pixel != ps.accPix) { flush(); ps.accPix = pixel; ps.acc0 = ps.acc1 = ps.acc2 = 0; }
+          if (pixel != tr.xw(XW_ACCPIX)) {
+            accFlush<T>(tr, a.out);
+            tr.xw(XW_ACCPIX) = pixel;
+            stD(&tr.xw(XW_ACC + 0), tr.stride, 0.0); stD(&tr.xw(XW_ACC + 2), tr.stride, 0.0); stD(&tr.xw(XW_ACC + 4), tr.stride, 0.0);
+          }
           ps.rng = streamGen(a.seed, pixel, s);
           ins.count(0);
           // uniformRandomUVs (Lib.hs:1362-1365): u = (x + ru)/W, v = (y + rv)/H with y counted from the bottom row
@@ -219,21 +253,23 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
           ps.phase = PH_MAIN; start = true;
           if (ps.depthLeft <= 0) { ps.phase = PH_IDLE; start = false; }  // rayColor with depth <= 0 is black (Lib.hs:1303-1304)
         }
-        const unsigned long long avail = cEnd - cNext; const unsigned n = __popc(idle);
-        cNext += (n < avail) ? n : avail;
-        idle = __ballot_sync(0xffffffffu, ps.phase == PH_IDLE);
+        const uint32_t avail = cEnd - cNext; const uint32_t n = (uint32_t)__popc(idle);
+        __syncwarp();
+        if (lane == 0) ws[2] = cNext + ((n < avail) ? n : avail);
+        __syncwarp();
+        idle = __ballot_sync(0xffffffffu, cls == 4 && ps.phase == PH_IDLE);
       }
       // ---- (3) start the next query: the bounce's `hit world` (Lib.hs:1309) or one `hit htbl (Ray o v 0)` of htblPdfValue (677)
       if (start) {
         ins.count(13);
         if (ps.phase == PH_MAIN) ins.count(1);
-        travBegin<T, FAST>(tr, ps.phase == PH_MAIN ? sc.world_root : ps.curLight, qo, qd, kEps<T>(), kInf<T>());
+        travBegin<T, FAST>(tr, ps.phase == PH_MAIN ? sc.world_root : tr.xu(X_CURLIGHT), qo, qd, kEps<T>(), kInf<T>());
       } else if (cls == 4) {
-        tr.cur = kEmpty;
+        tr.cur = kDead;  // only reached when the index space is exhausted
       }
     }
   }
-  flush();
+  accFlush<T>(tr, a.out);
   if constexpr (INSTR == 1) {
     for (int i = 0; i < 16; ++i) if (ins.c[i]) atomicAdd(a.ctr + i, (unsigned long long)ins.c[i]);
   }
@@ -256,11 +292,11 @@ __global__ void __launch_bounds__(kBlock) traceKernel(const __grid_constant__ DS
   travBegin<T, FAST>(tr, sc.world_root, o, d, (T)a.tmin, (T)a.tmax);
   travRun<T, S, 2, FAST>(sc, tr, time, rng, ins);
   a.nvisit[i] = ins.n; a.vhash[i] = ins.h;
-  a.hit[i] = tr.qhit ? 1 : 0;
+  a.hit[i] = tr.qhit() ? 1 : 0;
   double* out = a.rec + (size_t)i * 9;
-  if (tr.qhit) {
+  if (tr.qhit()) {
     HitRec<T> rec;
-    evalHit<T>(sc, o, d, time, tr.tbest, tr.bprim, tr.baux(), tr.bdepth(), &tr.x(X_BCHAIN), tr.stride, rec);
+    evalHit<T>(sc, o, d, time, tr.tbest, tr.bprim, tr.baux(), tr.bdepth(), &tr.xu(X_BCHAIN), tr.stride * (uint32_t)(sizeof(T) / 4), rec);
     out[0] = rec.t; out[1] = rec.p.x; out[2] = rec.p.y; out[3] = rec.p.z; out[4] = rec.n.x; out[5] = rec.n.y; out[6] = rec.n.z; out[7] = rec.u; out[8] = rec.v;
     a.prim[i] = tr.bprim; a.mat[i] = rec.mat; a.front[i] = rec.front ? 1 : 0;
   } else {
@@ -268,4 +304,3 @@ __global__ void __launch_bounds__(kBlock) traceKernel(const __grid_constant__ DS
     a.prim[i] = 0; a.mat[i] = kNone; a.front[i] = 0;
   }
 }
-

@@ -1,13 +1,13 @@
 // rt_traverse.cuh — `hit root ray t_min t_max` (Lib.hs:970-1109) as a resumable explicit-stack machine.
 //
-// The traversal state of one query lives in registers (Trav) plus a per-thread column of shared memory (stack + rarely
-// used frame / medium state), and advances by ONE step at a time:
+// The traversal state of one query lives in registers (Trav: scalars only, never address-taken) plus a per-thread column of
+// shared memory (stack + rarely used frame / medium / light-pdf / accumulator state), and advances by ONE step at a time:
 //     stepNode   : a BVHNode — the three independent slab tests (Lib.hs:798-814), then left child next, right child stacked
 //     stepSphere : a Sphere or MovingSphere leaf (one code path for both)
 //     stepRect   : a Rect or Cuboid leaf
 //     stepRare   : Translate / Rotate frames and their exit markers, ConstantMedium and its two boundary sub-queries,
 //                  Unhittable
-// so that the render kernel can schedule, per warp iteration, the step class most lanes are waiting for (rt_kernels.cuh).
+// so that the render kernel can run, per warp iteration, the step class most lanes are waiting for (rt_render_kernel.inl).
 // Per lane the sequence of steps is exactly the reference's evaluation order:
 //  * BVHNode (971-988): left first, then right with t_max := running closest t; any later accepted hit replaces the earlier
 //    one — a DFS with a running closest t in which every accepted primitive overwrites the record.
@@ -21,15 +21,27 @@
 
 namespace rtb {
 
-constexpr uint32_t kEmpty = 0xffffffffu;  // Trav::cur when the query has no step left
+constexpr uint32_t kEmpty = 0xffffffffu;  // Trav::cur when the query has no step left (kind 15)
+constexpr uint32_t kDead = 0xe0000000u;   // Trav::cur of a lane with no work left at all (kind 14)
 
-// shared-memory column layout (entry e of thread t at col[e * stride]); stack first, then the extras
-//   X_CHAIN..+3  open frames (transform refs)        X_BCHAIN..+3 frames of the best hit
-//   X_STMIN, X_STBEST, X_H1T (T, 2 words each)       X_WORLD..+11 world ray o,d (T, 2 words each) saved while frames are open
-constexpr int X_CHAIN = 0, X_BCHAIN = 4, X_STMIN = 8, X_STBEST = 10, X_H1T = 12, X_WORLD = 14, kExtraSlots = 26;
+// Shared-memory column of one thread: word e of thread t is col[e * blockDim.x].
+//   words [0, stackCap)             traversal stack
+//   words xbase + 0..5              radiance accumulator of the current pixel (3 doubles), xbase + 6 its pixel index
+//   words xbase + 8 + slot * w      "T slots" (w = sizeof(T)/4 words each; integers use the first word):
+constexpr int XW_ACC = 0, XW_ACCPIX = 6, XW_TSLOTS = 8;
+constexpr int X_CHAIN = 0;      // ..3   open frames (transform refs)
+constexpr int X_BCHAIN = 4;     // ..7   frames of the best hit
+constexpr int X_STMIN = 8, X_STBEST = 9, X_H1T = 10;   // outer query parked during a medium sub-query; first boundary hit
+constexpr int X_WORLD = 11;     // ..16  world ray o,d saved while frames are open
+constexpr int X_LSPDF = 17, X_LV2 = 18, X_LV1 = 19, X_CURW = 20;  // Lambertian mixture-pdf bookkeeping (Lib.hs:367-382, 823-836)
+constexpr int X_CURLIGHT = 21, X_LSP = 22;
+constexpr int X_LREF = 23;      // ..30  htblPdfValue walk stack: refs
+constexpr int X_LWT = 31;       // ..38  ... and their weights
+constexpr int kTSlots = 39;
+template <class T> __host__ __device__ constexpr int extraWords() { return XW_TSLOTS + kTSlots * (int)(sizeof(T) / 4); }
 
 // Trav::flags bit fields
-constexpr uint32_t F_INSUB = 1u, F_SQHIT = 2u;
+constexpr uint32_t F_INSUB = 1u, F_SQHIT = 2u, F_QHIT = 4u;
 constexpr int F_FD_SHIFT = 4, F_BDEPTH_SHIFT = 8, F_BAUX_SHIFT = 12;
 
 template <class T> struct Trav {
@@ -38,16 +50,17 @@ template <class T> struct Trav {
   T tmin, tbest;    // the query's t_min and its running closest t (t_max)
   uint32_t cur;     // next hittable ref / marker to process, kEmpty when done
   uint32_t bprim;   // primitive of the best hit (valid when qhit, outside sub-queries)
-  uint32_t flags;   // F_INSUB | F_SQHIT | fd << 4 | bdepth << 8 | baux << 12
+  uint32_t flags;   // F_INSUB | F_SQHIT | F_QHIT | fd << 4 | bdepth << 8 | baux << 12
   int sp;           // stack entries in use
-  bool qhit;
   uint32_t* col;    // this thread's shared-memory column
   uint32_t stride;  // threads per block
-  uint32_t xbase;   // first extra slot = stack capacity
+  uint32_t xbase;   // first extra word = stack capacity
 
   RTB_D void push(uint32_t v) { col[sp * stride] = v; ++sp; }
   RTB_D void next() { if (sp > 0) { --sp; cur = col[sp * stride]; } else cur = kEmpty; }
-  RTB_D uint32_t& x(int slot) { return col[(xbase + slot) * stride]; }
+  RTB_D uint32_t& xw(int word) { return col[(xbase + word) * stride]; }                                  // raw extra word
+  RTB_D uint32_t& xu(int slot) { return col[(xbase + XW_TSLOTS + slot * (int)(sizeof(T) / 4)) * stride]; }  // integer T slot
+  RTB_D bool qhit() const { return (flags & F_QHIT) != 0; }
   RTB_D int fd() const { return (int)((flags >> F_FD_SHIFT) & 7u); }
   RTB_D int bdepth() const { return (int)((flags >> F_BDEPTH_SHIFT) & 7u); }
   RTB_D uint32_t baux() const { return (flags >> F_BAUX_SHIFT) & 7u; }
@@ -58,6 +71,8 @@ RTB_D void stT(uint32_t* p, uint32_t stride, float v) { p[0] = __float_as_uint(v
 RTB_D void stT(uint32_t* p, uint32_t stride, double v) { unsigned long long b = (unsigned long long)__double_as_longlong(v); p[0] = (uint32_t)b; p[stride] = (uint32_t)(b >> 32); }
 RTB_D void ldT(const uint32_t* p, uint32_t stride, float& v) { v = __uint_as_float(p[0]); }
 RTB_D void ldT(const uint32_t* p, uint32_t stride, double& v) { v = __longlong_as_double((long long)((unsigned long long)p[0] | ((unsigned long long)p[stride] << 32))); }
+template <class T> RTB_D void xst(Trav<T>& tr, int slot, T v) { stT(&tr.xu(slot), tr.stride, v); }
+template <class T> RTB_D T xld(Trav<T>& tr, int slot) { T v; ldT(&tr.xu(slot), tr.stride, v); return v; }
 
 template <class T, bool FAST> RTB_D void setInv(Trav<T>& tr) {
   if (FAST) tr.inv = mk<T>((T)1 / tr.d.x, (T)1 / tr.d.y, (T)1 / tr.d.z);
@@ -67,17 +82,19 @@ template <class T, bool FAST> RTB_D void setInv(Trav<T>& tr) {
 template <class T, bool FAST>
 RTB_D void travBegin(Trav<T>& tr, uint32_t root, const V3<T>& o, const V3<T>& d, T t_min, T t_max) {
   tr.o = o; tr.d = d; setInv<T, FAST>(tr);
-  tr.tmin = t_min; tr.tbest = t_max; tr.cur = root; tr.bprim = 0; tr.flags = 0; tr.sp = 0; tr.qhit = false;
+  tr.tmin = t_min; tr.tbest = t_max; tr.cur = root; tr.bprim = 0; tr.flags = 0; tr.sp = 0;
 }
 
 // an accepted primitive hit replaces the record (Lib.hs:979-987)
 template <class T> RTB_D void travAccept(Trav<T>& tr, T t, uint32_t ref, uint32_t aux) {
-  tr.tbest = t; tr.qhit = true;
+  tr.tbest = t;
   if (!(tr.flags & F_INSUB)) {
-    const int fd = tr.fd();
+    const uint32_t fd = (tr.flags >> F_FD_SHIFT) & 7u;
     tr.bprim = ref;
-    tr.flags = (tr.flags & 0xffu) | ((uint32_t)fd << F_BDEPTH_SHIFT) | (aux << F_BAUX_SHIFT);
-    for (int i = 0; i < fd; ++i) tr.x(X_BCHAIN + i) = tr.x(X_CHAIN + i);
+    tr.flags = (tr.flags & 0xffu) | F_QHIT | (fd << F_BDEPTH_SHIFT) | (aux << F_BAUX_SHIFT);
+    for (uint32_t i = 0; i < fd; ++i) tr.xu(X_BCHAIN + (int)i) = tr.xu(X_CHAIN + (int)i);
+  } else {
+    tr.flags |= F_QHIT;
   }
 }
 
@@ -111,29 +128,16 @@ RTB_D void stepSphere(const DScene<T>& sc, Trav<T>& tr, T time, Instr<INSTR>& in
   tr.next();
 }
 
-// restore the current-frame ray after a frame exit: depth 0 = the saved world ray, else replay the open chain
-template <class T, bool FAST> RTB_D void travReframe(const DScene<T>& sc, Trav<T>& tr) {
-  const int fd = tr.fd();
-  const int w = sizeof(T) / 4;
-  T v[6];
-  for (int i = 0; i < 6; ++i) ldT(&tr.x(X_WORLD + i * w), tr.stride, v[i]);
-  tr.o = mk<T>(v[0], v[1], v[2]); tr.d = mk<T>(v[3], v[4], v[5]);
-  for (int i = 0; i < fd; ++i) applyXform<T>(sc, tr.x(X_CHAIN + i), tr.o, tr.d);
-  setInv<T, FAST>(tr);
-}
-
 // Rect and Cuboid leaves
 template <class T, int INSTR>
 RTB_D void stepRect(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
   const uint32_t ref = tr.cur, kind = ref >> 28, idx = ref & 0x0fffffffu;
+  ins.visit(ref);
   if (kind != K_CUBOID) {
-    ins.visit(ref);
     const Q4<T> a = ldq(sc.rects + 2 * (size_t)idx), b = ldq(sc.rects + 2 * (size_t)idx + 1);
     T t;
     if (rectT<T>(kind - K_RECT_XY, a.x, a.y, a.z, a.w, b.x, tr.o, tr.d, tr.tmin, tr.tbest, t)) travAccept<T>(tr, t, ref, 0);
-    tr.next();
-  } else if (kind == K_CUBOID) {  // Lib.hs:989-1004: foldr over the six rects => last first; strict `<` replaces
-    ins.visit(ref);
+  } else {  // Lib.hs:989-1004: foldr over the six rects => last first; strict `<` replaces
     const Q4<T> mn = ldq(sc.cuboids + 2 * (size_t)idx), mx = ldq(sc.cuboids + 2 * (size_t)idx + 1);
     bool acc = false; T tNew = 0; uint32_t aux = 0;
 #pragma unroll
@@ -146,24 +150,32 @@ RTB_D void stepRect(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
       }
     }
     if (acc) travAccept<T>(tr, tNew, ref, aux);
-    tr.next();
   }
+  tr.next();
 }
 
-// the rare kinds: frames, markers, media, Unhittable (kept out of line: the hot loop stays small)
+// restore the current-frame ray after a frame exit: the saved world ray, then replay the chain of still-open frames
+template <class T, bool FAST> RTB_D void travReframe(const DScene<T>& sc, Trav<T>& tr) {
+  const int fd = tr.fd();
+  tr.o = mk<T>(xld<T>(tr, X_WORLD + 0), xld<T>(tr, X_WORLD + 1), xld<T>(tr, X_WORLD + 2));
+  tr.d = mk<T>(xld<T>(tr, X_WORLD + 3), xld<T>(tr, X_WORLD + 4), xld<T>(tr, X_WORLD + 5));
+  for (int i = 0; i < fd; ++i) applyXform<T>(sc, tr.xu(X_CHAIN + i), tr.o, tr.d);
+  setInv<T, FAST>(tr);
+}
+
+// the rare kinds: frames, markers, media, Unhittable
 template <class T, int INSTR, bool FAST>
-__device__ __noinline__ void stepRare(const DScene<T>& sc, Trav<T>& tr, Rng& rng, Instr<INSTR>& ins) {
+RTB_D void stepRare(const DScene<T>& sc, Trav<T>& tr, Rng& rng, Instr<INSTR>& ins) {
   const uint32_t ref = tr.cur, kind = ref >> 28, idx = ref & 0x0fffffffu;
-  const int w = sizeof(T) / 4;
   if (kind == K_TRANSLATE || kind == K_ROTATE) {
     ins.visit(ref);
     const uint32_t child = (kind == K_TRANSLATE) ? bitsOf(ldq(sc.translates + idx).w) : bitsOf(ldq(sc.rotates + idx).w);
     const int fd = tr.fd();
     if (fd == 0) {  // park the world ray: restoring it must be exact, not (o - off) + off
-      const T v[6] = {tr.o.x, tr.o.y, tr.o.z, tr.d.x, tr.d.y, tr.d.z};
-      for (int i = 0; i < 6; ++i) stT(&tr.x(X_WORLD + i * w), tr.stride, v[i]);
+      xst<T>(tr, X_WORLD + 0, tr.o.x); xst<T>(tr, X_WORLD + 1, tr.o.y); xst<T>(tr, X_WORLD + 2, tr.o.z);
+      xst<T>(tr, X_WORLD + 3, tr.d.x); xst<T>(tr, X_WORLD + 4, tr.d.y); xst<T>(tr, X_WORLD + 5, tr.d.z);
     }
-    tr.x(X_CHAIN + fd) = ref;
+    tr.xu(X_CHAIN + fd) = ref;
     tr.setFd(fd + 1);
     applyXform<T>(sc, ref, tr.o, tr.d);
     setInv<T, FAST>(tr);
@@ -175,28 +187,28 @@ __device__ __noinline__ void stepRare(const DScene<T>& sc, Trav<T>& tr, Rng& rng
     tr.next();
   } else if (kind == K_MEDIUM) {  // Lib.hs:1054: hit boundary ray (-inf) inf
     ins.visit(ref);
-    stT(&tr.x(X_STMIN), tr.stride, tr.tmin); stT(&tr.x(X_STBEST), tr.stride, tr.tbest);
-    tr.flags = (tr.flags & ~F_SQHIT) | F_INSUB | (tr.qhit ? F_SQHIT : 0u);
-    tr.tmin = -kInf<T>(); tr.tbest = kInf<T>(); tr.qhit = false;
+    xst<T>(tr, X_STMIN, tr.tmin); xst<T>(tr, X_STBEST, tr.tbest);
+    tr.flags = (tr.flags & ~(F_SQHIT | F_QHIT)) | F_INSUB | ((tr.flags & F_QHIT) ? F_SQHIT : 0u);
+    tr.tmin = -kInf<T>(); tr.tbest = kInf<T>();
     tr.push((K_MARK_MED1 << 28) | idx);
     tr.cur = bitsOf(ldq(sc.media + idx).z);
   } else if (kind == K_MARK_MED1) {
-    if (!tr.qhit) {
-      ldT(&tr.x(X_STMIN), tr.stride, tr.tmin); ldT(&tr.x(X_STBEST), tr.stride, tr.tbest);
-      tr.qhit = (tr.flags & F_SQHIT) != 0; tr.flags &= ~F_INSUB;
+    if (!tr.qhit()) {
+      tr.tmin = xld<T>(tr, X_STMIN); tr.tbest = xld<T>(tr, X_STBEST);
+      tr.flags = (tr.flags & ~(F_INSUB | F_QHIT | F_SQHIT)) | ((tr.flags & F_SQHIT) ? F_QHIT : 0u);
       tr.next();
     } else {  // Lib.hs:1057: hit boundary ray (h1t + epsilon) inf
-      stT(&tr.x(X_H1T), tr.stride, tr.tbest);
-      tr.tmin = tr.tbest + kEps<T>(); tr.tbest = kInf<T>(); tr.qhit = false;
+      xst<T>(tr, X_H1T, tr.tbest);
+      tr.tmin = tr.tbest + kEps<T>(); tr.tbest = kInf<T>(); tr.flags &= ~F_QHIT;
       tr.push((K_MARK_MED2 << 28) | idx);
       tr.cur = bitsOf(ldq(sc.media + idx).z);
     }
   } else if (kind == K_MARK_MED2) {
-    const bool h2 = tr.qhit; const T h2t = tr.tbest;
-    ldT(&tr.x(X_STMIN), tr.stride, tr.tmin); ldT(&tr.x(X_STBEST), tr.stride, tr.tbest);
-    tr.qhit = (tr.flags & F_SQHIT) != 0; tr.flags &= ~F_INSUB;
+    const bool h2 = tr.qhit(); const T h2t = tr.tbest;
+    tr.tmin = xld<T>(tr, X_STMIN); tr.tbest = xld<T>(tr, X_STBEST);
+    tr.flags = (tr.flags & ~(F_INSUB | F_QHIT | F_SQHIT)) | ((tr.flags & F_SQHIT) ? F_QHIT : 0u);
     if (h2) {  // Lib.hs:1060-1079
-      T h1t; ldT(&tr.x(X_H1T), tr.stride, h1t);
+      const T h1t = xld<T>(tr, X_H1T);
       const T rec1t_ = hmax(tr.tmin, h1t);
       const T rec2t = hmin(tr.tbest, h2t);
       if (!(rec1t_ >= rec2t)) {
@@ -215,10 +227,10 @@ __device__ __noinline__ void stepRare(const DScene<T>& sc, Trav<T>& tr, Rng& rng
   }
 }
 
-// step class of a lane's pending work: 0 node, 1 sphere-like leaf, 2 rect / cuboid leaf, 3 rare
+// step class of a lane's pending work: 0 node, 1 sphere-like leaf, 2 rect / cuboid leaf, 3 rare, 4 query finished (kEmpty),
+// 5 dead lane (kDead); one nibble per kind
 RTB_D int stepClass(uint32_t cur) {
-  const uint32_t k = cur >> 28;
-  return k == K_BVH ? 0 : ((k == K_SPHERE || k == K_MOVING) ? 1 : ((k >= K_RECT_XY && k <= K_CUBOID) ? 2 : 3));
+  return (int)((0x4533333302222113ULL >> ((cur >> 28) * 4u)) & 0xfULL);
 }
 
 // run a whole query to completion (K1 and the texture-free probes): same steps, no scheduling

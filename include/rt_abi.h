@@ -227,6 +227,11 @@ int rt_texture_value(rt_scene_t scene, uint32_t tex, uint32_t precision, uint32_
  * in: host double[n] sums; out: host uint8[n].  NaN maps to 0 (GHC's floor NaN :: Word8 is platform-defined). */
 int rt_tonemap(const double* rgb_sum, uint32_t n, uint32_t total_samples, uint8_t* out_rgb8);
 
+/* Device self-test of the literal fp32 build's slab-test division (the hoisted-reciprocal form of the compiler's own IEEE
+ * sequence, rt_device.cuh): n random operand pairs of the validated range against __fdiv_rn; bit-exactness requires
+ * *mismatches == 0.  Not part of the reference path. */
+int rt_selftest_division(uint64_t n, uint64_t seed, uint64_t* checked, uint64_t* mismatches);
+
 void rt_shutdown(void);
 
 #ifdef __cplusplus

@@ -6,6 +6,8 @@
 #include "rt_device.cuh"
 #include "rt_launch.h"
 
+#include <algorithm>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -219,6 +221,8 @@ template <class T> int buildDevice(const HostScene& h, DevBuffers<T>& db) {
   }
   if ((rc = upload(db, imgs, &sc.images))) return rc;
   sc.world_root = h.world_root; sc.lights_root = h.lights_root;
+  sc.bigCoords = 0; sc.pad_ = 0;
+  for (double v : h.node_box) if (!(std::fabs(v) <= 1099511627776.0)) sc.bigCoords = 1;  // beyond 2^40 or non-finite (rt_device.cuh kDivHi)
   for (int i = 0; i < 3; ++i) sc.bg[i] = (T)h.background[i];
   for (int i = 0; i < 24; ++i) sc.cam[i] = (T)h.camera[i];
   db.ready = true;
@@ -275,7 +279,7 @@ int renderLaunch(SceneEntry* e, const RtRenderParams& q, double* d_out, cudaStre
   unsigned long long chunk = 1024;
   while (chunk > 64 && a.total_paths / chunk < warps * 8ull) chunk /= 2;
   a.chunk = (uint32_t)chunk;
-  a.shadeMin = tuneParam("RTB_SHADE_MIN", 8); a.keepNode = tuneParam("RTB_KEEP_NODE", 16); a.keepLeaf = tuneParam("RTB_KEEP_LEAF", 16);
+  a.shadeMin = tuneParam("RTB_SHADE_MIN", 8); a.keepNode = std::max(1u, tuneParam("RTB_KEEP_NODE", 16)); a.keepLeaf = std::max(1u, tuneParam("RTB_KEEP_LEAF", 12));
   a.counter = e->d_counter; a.ctr = counted ? e->d_counter + 1 : nullptr; a.out = d_out;
   cudaError_t ce = (q.flags & RT_FLAG_FAST_MATH) ? launchRender<true>((int)q.precision, counted ? 1 : 0, dsc, a, e->hs.stackDepth, e->numSMs, st, gridOut)
                                                  : launchRender<false>((int)q.precision, counted ? 1 : 0, dsc, a, e->hs.stackDepth, e->numSMs, st, gridOut);
@@ -563,6 +567,22 @@ int rt_tonemap(const double* rgb_sum, uint32_t n, uint32_t total_samples, uint8_
   if (ce == cudaSuccess) ce = cudaMemcpy(out_rgb8, dout, n, cudaMemcpyDeviceToHost);
   cudaFree(din); cudaFree(dout);
   if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("tonemap: ") + cudaGetErrorString(ce));
+  return RT_OK;
+}
+
+int rt_selftest_division(uint64_t n, uint64_t seed, uint64_t* checked, uint64_t* mismatches) {
+  if (!checked || !mismatches) return fail(RT_ERR_ARG, "null output");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(RT_ERR_CUDA, "no CUDA device available (this library has no CPU path)"); }
+  unsigned long long* d = nullptr;
+  CU(cudaMalloc(&d, 2 * sizeof(unsigned long long)));
+  CU(cudaMemset(d, 0, 2 * sizeof(unsigned long long)));
+  cudaError_t ce = launchDivSelftest(n, seed, d, 0);
+  unsigned long long h[2] = {0, 0};
+  if (ce == cudaSuccess) ce = cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("division selftest: ") + cudaGetErrorString(ce));
+  *checked = h[0]; *mismatches = h[1];
   return RT_OK;
 }
 

@@ -14,7 +14,6 @@
 
 namespace rtb {
 
-constexpr int kBlock = 128;
 
 template <class T> struct MinBlocks { static constexpr int v = 4; };
 template <> struct MinBlocks<double> { static constexpr int v = 1; };

@@ -13,7 +13,7 @@ struct RenderArgs {
   uint32_t chunk;                  // path indices a warp takes per atomic
   uint32_t stackCap;               // traversal stack entries per thread (set by the launcher)
   uint32_t shadeMin;               // run the shade class as soon as this many lanes wait for it
-  uint32_t keepNode, keepLeaf;     // stay in the node / sphere inner loop while more than live * keep / 32 lanes remain in the class
+  uint32_t keepNode, keepLeaf;     // run a node / sphere step without a full vote when at least this many lanes wait for one
   unsigned long long seed;
   unsigned long long total_paths;  // region pixels * ns
   unsigned long long* counter;     // device: next free path index
@@ -35,6 +35,7 @@ struct TraceArgs {
 template <bool FAST> cudaError_t launchRender(int prec, int instr, const void* dscene, const RenderArgs& a, int stackDepth, int numSMs, cudaStream_t st, int* gridOut);
 template <bool FAST> cudaError_t launchTrace(int prec, const void* dscene, const TraceArgs& a, int stackDepth, cudaStream_t st);
 cudaError_t launchTexture(int prec, const void* dscene, uint32_t tex, uint32_t n, const double* q, double* out, cudaStream_t st);
+cudaError_t launchDivSelftest(unsigned long long n, unsigned long long seed, unsigned long long* out2, cudaStream_t st);
 cudaError_t launchTonemap(const double* sum, uint32_t n, double ns, uint8_t* out, cudaStream_t st);
 
 }  // namespace rtb

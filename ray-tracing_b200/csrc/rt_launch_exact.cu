@@ -13,6 +13,31 @@ static __global__ void tonemapKernel(const double* sum, uint32_t n, double ns, u
   out[i] = (f == f) ? (uint8_t)(int)f : (uint8_t)0;
 }
 
+// divByRcp(a, d, rcpRefined(d)) against the IEEE quotient over random operands of the validated range (rt_device.cuh)
+static __global__ void divSelftestKernel(unsigned long long n, unsigned long long seed, unsigned long long* out2) {
+  const unsigned long long tid = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x, nthreads = (unsigned long long)gridDim.x * blockDim.x;
+  Rng g = streamGen(seed, (uint32_t)tid, (uint32_t)(tid >> 32));
+  unsigned long long checked = 0, bad = 0;
+  for (unsigned long long i = tid; i < n; i += nthreads) {
+    const unsigned long long w = nextWord(g), w2 = nextWord(g);
+    // d: sign, exponent 2^-40 .. 2^39, random mantissa; a: sign, exponent 2^-90 .. 2^40, random mantissa
+    const uint32_t db = ((uint32_t)(w >> 63) << 31) | ((87u + (uint32_t)((w >> 32) % 80u)) << 23) | ((uint32_t)w & 0x7fffffu);
+    const uint32_t ab = ((uint32_t)(w2 >> 63) << 31) | ((37u + (uint32_t)((w2 >> 32) % 131u)) << 23) | ((uint32_t)w2 & 0x7fffffu);
+    float d = __uint_as_float(db), a = __uint_as_float(ab);
+    if ((i & 7u) == 0u) a = d * (float)(int)((w2 >> 40) & 1023u);  // exact and near-exact quotients
+    if (!(fabsf(d) >= kDivLo && fabsf(d) <= kDivHi)) continue;
+    const float q = divByRcp(a, d, rcpRefined(d));
+    if (!(fabsf(q) >= kDivLo)) continue;  // outside the validated range: the kernels take the generic division
+    ++checked;
+    if (__float_as_uint(q) != __float_as_uint(__fdiv_rn(a, d))) ++bad;
+  }
+  atomicAdd(out2, checked); atomicAdd(out2 + 1, bad);
+}
+cudaError_t launchDivSelftest(unsigned long long n, unsigned long long seed, unsigned long long* out2, cudaStream_t st) {
+  divSelftestKernel<<<148 * 8, 256, 0, st>>>(n, seed, out2);
+  return cudaGetLastError();
+}
+
 template cudaError_t launchRender<false>(int, int, const void*, const RenderArgs&, int, int, cudaStream_t, int*);
 template cudaError_t launchTrace<false>(int, const void*, const TraceArgs&, int, cudaStream_t);
 

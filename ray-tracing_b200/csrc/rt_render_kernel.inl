@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
   if constexpr (INSTR == 1) ins.init();
 
   Trav<T> tr;
-  tr.col = smem + threadIdx.x; tr.stride = blockDim.x; tr.xbase = a.stackCap;
+  tr.col = smem + threadIdx.x;
   tr.cur = kEmpty; tr.sp = 0; tr.flags = 0; tr.bprim = 0; tr.tmin = 0; tr.tbest = 0;
   tr.o = mk<T>(0, 0, 0); tr.d = mk<T>(0, 0, 1); tr.inv = mk<T>(0, 0, 0);
   PathState<T> ps;
@@ -170,36 +170,33 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
   const uint32_t regionW = a.col1 - a.col0;
 
   for (;;) {
-    // ---- classify this lane's pending work and vote
+    // ---- fast votes: a node step when at least keepNode lanes wait for one, else a sphere step when keepLeaf lanes do;
+    //      otherwise the full vote: the class most lanes wait for, shade as soon as shadeMin lanes wait for it
+    const uint32_t kind = tr.cur >> 28;
+    const bool isNode = kind == K_BVH, isLeaf = kind == K_SPHERE || kind == K_MOVING;
     const int cls = stepClass(tr.cur);
-    const unsigned m0 = __ballot_sync(0xffffffffu, cls == 0), m1 = __ballot_sync(0xffffffffu, cls == 1), m2 = __ballot_sync(0xffffffffu, cls == 2),
-                   m3 = __ballot_sync(0xffffffffu, cls == 3), m4 = __ballot_sync(0xffffffffu, cls == 4);
-    const unsigned live = m0 | m1 | m2 | m3 | m4;
-    if (live == 0u) break;
-    const int c0 = __popc(m0), c1 = __popc(m1), c2 = __popc(m2), c3 = __popc(m3), c4 = __popc(m4);
-    int pick = 0, best = c0;
-    if (c1 > best) { pick = 1; best = c1; }
-    if (c2 > best) { pick = 2; best = c2; }
-    if (c3 > best) { pick = 3; best = c3; }
-    if (c4 > best || c4 >= (int)a.shadeMin) pick = 4;
+    int pick = 0;
+    const int cN = __popc(__ballot_sync(0xffffffffu, isNode));
+    if (cN < (int)a.keepNode) {
+      const int cL = __popc(__ballot_sync(0xffffffffu, isLeaf));
+      pick = 1;
+      if (cL < (int)a.keepLeaf) {
+        const int c2 = __popc(__ballot_sync(0xffffffffu, cls == 2)), c3 = __popc(__ballot_sync(0xffffffffu, cls == 3)),
+                  c4 = __popc(__ballot_sync(0xffffffffu, cls == 4));
+        if ((cN | cL | c2 | c3 | c4) == 0) break;
+        int best = cN;
+        pick = 0;
+        if (cL > best) { pick = 1; best = cL; }
+        if (c2 > best) { pick = 2; best = c2; }
+        if (c3 > best) { pick = 3; best = c3; }
+        if (c4 > best || c4 >= (int)a.shadeMin) pick = 4;
+      }
+    }
 
-    if (pick == 0) {  // stay on node steps while enough lanes remain in the class
-      const int keep = (__popc(live) * (int)a.keepNode) >> 5;
-      int n;
-      do {
-        if ((tr.cur >> 28) == K_BVH) stepNode<T, INSTR, FAST>(sc, tr, ins);
-        n = __popc(__ballot_sync(0xffffffffu, (tr.cur >> 28) == K_BVH));
-      } while (n > keep);
+    if (pick == 0) {
+      if (isNode) stepNode<T, INSTR, FAST>(sc, tr, ins);
     } else if (pick == 1) {
-      const T qtime = (ps.phase == PH_MAIN) ? ps.time : (T)0;  // htblPdfValue traces with time 0 (Lib.hs:677)
-      const int keep = (__popc(live) * (int)a.keepLeaf) >> 5;
-      int n;
-      do {
-        const uint32_t k = tr.cur >> 28;
-        if (k == K_SPHERE || k == K_MOVING) stepSphere<T, S, INSTR>(sc, tr, qtime, ins);
-        const uint32_t k2 = tr.cur >> 28;
-        n = __popc(__ballot_sync(0xffffffffu, k2 == K_SPHERE || k2 == K_MOVING));
-      } while (n > keep);
+      if (isLeaf) stepSphere<T, S, INSTR>(sc, tr, (ps.phase == PH_MAIN) ? ps.time : (T)0, ins);  // htblPdfValue traces with time 0 (Lib.hs:677)
     } else if (pick == 2) {
       if (cls == 2) stepRect<T, INSTR>(sc, tr, ins);
     } else if (pick == 3) {
@@ -263,7 +260,7 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
       if (start) {
         ins.count(13);
         if (ps.phase == PH_MAIN) ins.count(1);
-        travBegin<T, FAST>(tr, ps.phase == PH_MAIN ? sc.world_root : tr.xu(X_CURLIGHT), qo, qd, kEps<T>(), kInf<T>());
+        travBegin<T, FAST>(sc, tr, ps.phase == PH_MAIN ? sc.world_root : tr.xu(X_CURLIGHT), qo, qd, kEps<T>(), kInf<T>());
       } else if (cls == 4) {
         tr.cur = kDead;  // only reached when the index space is exhausted
       }
@@ -288,8 +285,8 @@ __global__ void __launch_bounds__(kBlock) traceKernel(const __grid_constant__ DS
   Instr<2> ins; ins.init(a.vlog + (size_t)i * a.logStride, a.logStride);
   for (uint32_t k = 0; k < a.logStride; ++k) a.vlog[(size_t)i * a.logStride + k] = kNone;
   Trav<T> tr;
-  tr.col = smem + threadIdx.x; tr.stride = blockDim.x; tr.xbase = a.stackCap;
-  travBegin<T, FAST>(tr, sc.world_root, o, d, (T)a.tmin, (T)a.tmax);
+  tr.col = smem + threadIdx.x;
+  travBegin<T, FAST>(sc, tr, sc.world_root, o, d, (T)a.tmin, (T)a.tmax);
   travRun<T, S, 2, FAST>(sc, tr, time, rng, ins);
   a.nvisit[i] = ins.n; a.vhash[i] = ins.h;
   a.hit[i] = tr.qhit() ? 1 : 0;

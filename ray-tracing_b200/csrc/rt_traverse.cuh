@@ -24,10 +24,12 @@ namespace rtb {
 constexpr uint32_t kEmpty = 0xffffffffu;  // Trav::cur when the query has no step left (kind 15)
 constexpr uint32_t kDead = 0xe0000000u;   // Trav::cur of a lane with no work left at all (kind 14)
 
-// Shared-memory column of one thread: word e of thread t is col[e * blockDim.x].
-//   words [0, stackCap)             traversal stack
-//   words xbase + 0..5              radiance accumulator of the current pixel (3 doubles), xbase + 6 its pixel index
-//   words xbase + 8 + slot * w      "T slots" (w = sizeof(T)/4 words each; integers use the first word):
+constexpr int kBlock = 128;               // threads per block of every kernel that owns shared-memory columns
+
+// Shared-memory column of one thread: word e of thread t is col[e * kBlock] (compile-time stride and offsets).
+//   words 0..5                      radiance accumulator of the current pixel (3 doubles), word 6 its pixel index
+//   words 8 + slot * w              "T slots" (w = sizeof(T)/4 words each; integers use the first word):
+//   words extraWords<T>() + [0, stackCap)   traversal stack
 constexpr int XW_ACC = 0, XW_ACCPIX = 6, XW_TSLOTS = 8;
 constexpr int X_CHAIN = 0;      // ..3   open frames (transform refs)
 constexpr int X_BCHAIN = 4;     // ..7   frames of the best hit
@@ -41,25 +43,27 @@ constexpr int kTSlots = 39;
 template <class T> __host__ __device__ constexpr int extraWords() { return XW_TSLOTS + kTSlots * (int)(sizeof(T) / 4); }
 
 // Trav::flags bit fields
-constexpr uint32_t F_INSUB = 1u, F_SQHIT = 2u, F_QHIT = 4u;
+constexpr uint32_t F_INSUB = 1u, F_SQHIT = 2u, F_QHIT = 4u, F_NANT = 8u;  // F_NANT: a NaN t was accepted (rect with d_k = 0, o_k = k)
 constexpr int F_FD_SHIFT = 4, F_BDEPTH_SHIFT = 8, F_BAUX_SHIFT = 12;
+constexpr int F_MODE_SHIFT = 16;  // 2 bits per axis: division mode of the slab test (rt_device.cuh slabMode), literal fp32 build only
+constexpr uint32_t F_MODE_MASK = 63u << F_MODE_SHIFT, F_MODE_GENERIC = (2u | (2u << 2) | (2u << 4)) << F_MODE_SHIFT;
 
 template <class T> struct Trav {
   V3<T> o, d;       // ray in the current frame
-  V3<T> inv;        // 1/d (FAST only)
+  V3<T> inv;        // FAST: 1/d; literal fp32: the refined reciprocal (or +-inf) of the axis' division mode
   T tmin, tbest;    // the query's t_min and its running closest t (t_max)
   uint32_t cur;     // next hittable ref / marker to process, kEmpty when done
   uint32_t bprim;   // primitive of the best hit (valid when qhit, outside sub-queries)
-  uint32_t flags;   // F_INSUB | F_SQHIT | F_QHIT | fd << 4 | bdepth << 8 | baux << 12
+  uint32_t flags;   // F_INSUB | F_SQHIT | F_QHIT | F_NANT | fd << 4 | bdepth << 8 | baux << 12 | axis modes << 16
   int sp;           // stack entries in use
   uint32_t* col;    // this thread's shared-memory column
-  uint32_t stride;  // threads per block
-  uint32_t xbase;   // first extra word = stack capacity
+  static constexpr uint32_t stride = kBlock;
+  static constexpr int kStackBase = XW_TSLOTS + kTSlots * (int)(sizeof(T) / 4);
 
-  RTB_D void push(uint32_t v) { col[sp * stride] = v; ++sp; }
-  RTB_D void next() { if (sp > 0) { --sp; cur = col[sp * stride]; } else cur = kEmpty; }
-  RTB_D uint32_t& xw(int word) { return col[(xbase + word) * stride]; }                                  // raw extra word
-  RTB_D uint32_t& xu(int slot) { return col[(xbase + XW_TSLOTS + slot * (int)(sizeof(T) / 4)) * stride]; }  // integer T slot
+  RTB_D void push(uint32_t v) { col[(kStackBase + sp) * stride] = v; ++sp; }
+  RTB_D void next() { if (sp > 0) { --sp; cur = col[(kStackBase + sp) * stride]; } else cur = kEmpty; }
+  RTB_D uint32_t& xw(int word) { return col[word * stride]; }                                            // raw extra word
+  RTB_D uint32_t& xu(int slot) { return col[(XW_TSLOTS + slot * (int)(sizeof(T) / 4)) * stride]; }       // integer T slot
   RTB_D bool qhit() const { return (flags & F_QHIT) != 0; }
   RTB_D int fd() const { return (int)((flags >> F_FD_SHIFT) & 7u); }
   RTB_D int bdepth() const { return (int)((flags >> F_BDEPTH_SHIFT) & 7u); }
@@ -74,24 +78,40 @@ RTB_D void ldT(const uint32_t* p, uint32_t stride, double& v) { v = __longlong_a
 template <class T> RTB_D void xst(Trav<T>& tr, int slot, T v) { stT(&tr.xu(slot), tr.stride, v); }
 template <class T> RTB_D T xld(Trav<T>& tr, int slot) { T v; ldT(&tr.xu(slot), tr.stride, v); return v; }
 
-template <class T, bool FAST> RTB_D void setInv(Trav<T>& tr) {
-  if (FAST) tr.inv = mk<T>((T)1 / tr.d.x, (T)1 / tr.d.y, (T)1 / tr.d.z);
+RTB_D void axisMode(float d, bool oSafe, float& r, uint32_t& mode) {
+  const float ad = fabsf(d);
+  if (oSafe && ad >= kDivLo && ad <= kDivHi) { r = rcpRefined(d); mode = 0u; }
+  else if (d == 0.0f) { r = copysignf(__int_as_float(0x7f800000), d); mode = 1u; }
+  else { r = 0.0f; mode = 2u; }
+}
+// per-ray (per frame) setup of the slab test's divisions
+template <class T, bool FAST> RTB_D void setInv(const DScene<T>& sc, Trav<T>& tr) {
+  if constexpr (FAST) {
+    tr.inv = mk<T>((T)1 / tr.d.x, (T)1 / tr.d.y, (T)1 / tr.d.z);
+  } else if constexpr (sizeof(T) == 4) {
+    const bool oSafe = !sc.bigCoords && !(tr.flags & F_NANT) && fabsf(tr.o.x) <= kDivHi && fabsf(tr.o.y) <= kDivHi && fabsf(tr.o.z) <= kDivHi;
+    uint32_t mx, my, mz;
+    axisMode(tr.d.x, oSafe, tr.inv.x, mx); axisMode(tr.d.y, oSafe, tr.inv.y, my); axisMode(tr.d.z, oSafe, tr.inv.z, mz);
+    tr.flags = (tr.flags & ~F_MODE_MASK) | ((mx | (my << 2) | (mz << 4)) << F_MODE_SHIFT);
+  }
 }
 
 // start `hit root (Ray o d _) t_min t_max`
 template <class T, bool FAST>
-RTB_D void travBegin(Trav<T>& tr, uint32_t root, const V3<T>& o, const V3<T>& d, T t_min, T t_max) {
-  tr.o = o; tr.d = d; setInv<T, FAST>(tr);
-  tr.tmin = t_min; tr.tbest = t_max; tr.cur = root; tr.bprim = 0; tr.flags = 0; tr.sp = 0;
+RTB_D void travBegin(const DScene<T>& sc, Trav<T>& tr, uint32_t root, const V3<T>& o, const V3<T>& d, T t_min, T t_max) {
+  tr.o = o; tr.d = d; tr.flags = (t_max == t_max) ? 0u : F_NANT;
+  setInv<T, FAST>(sc, tr);
+  tr.tmin = t_min; tr.tbest = t_max; tr.cur = root; tr.bprim = 0; tr.sp = 0;
 }
 
 // an accepted primitive hit replaces the record (Lib.hs:979-987)
 template <class T> RTB_D void travAccept(Trav<T>& tr, T t, uint32_t ref, uint32_t aux) {
   tr.tbest = t;
+  if (!(t == t)) tr.flags |= F_NANT | F_MODE_GENERIC;  // a NaN t_max: only the literal slab test is right from here on
   if (!(tr.flags & F_INSUB)) {
     const uint32_t fd = (tr.flags >> F_FD_SHIFT) & 7u;
     tr.bprim = ref;
-    tr.flags = (tr.flags & 0xffu) | F_QHIT | (fd << F_BDEPTH_SHIFT) | (aux << F_BAUX_SHIFT);
+    tr.flags = (tr.flags & 0xffff00ffu) | F_QHIT | (fd << F_BDEPTH_SHIFT) | (aux << F_BAUX_SHIFT);
     for (uint32_t i = 0; i < fd; ++i) tr.xu(X_BCHAIN + (int)i) = tr.xu(X_CHAIN + (int)i);
   } else {
     tr.flags |= F_QHIT;
@@ -103,9 +123,23 @@ RTB_D void stepNode(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
   const uint32_t idx = tr.cur & 0x0fffffffu;
   ins.visit(tr.cur); ins.boxTest();
   const Q4<T> lo = ldq(sc.nodes + 2 * (size_t)idx), hi = ldq(sc.nodes + 2 * (size_t)idx + 1);
-  const bool bx = slab<T, FAST>(lo.x, hi.x, tr.o.x, tr.d.x, tr.inv.x, tr.tmin, tr.tbest);
-  const bool by = slab<T, FAST>(lo.y, hi.y, tr.o.y, tr.d.y, tr.inv.y, tr.tmin, tr.tbest);
-  const bool bz = slab<T, FAST>(lo.z, hi.z, tr.o.z, tr.d.z, tr.inv.z, tr.tmin, tr.tbest);
+  bool bx, by, bz;
+  if constexpr (!FAST && sizeof(T) == 4) {
+    const uint32_t md = tr.flags >> F_MODE_SHIFT;
+    bool ok = true;
+    bx = slabMode(md & 3u, lo.x, hi.x, tr.o.x, tr.d.x, tr.inv.x, tr.tmin, tr.tbest, ok);
+    by = slabMode((md >> 2) & 3u, lo.y, hi.y, tr.o.y, tr.d.y, tr.inv.y, tr.tmin, tr.tbest, ok);
+    bz = slabMode((md >> 4) & 3u, lo.z, hi.z, tr.o.z, tr.d.z, tr.inv.z, tr.tmin, tr.tbest, ok);
+    if (!ok) {  // a quotient left the validated range of the hoisted reciprocal (e.g. an exact 0): the generic divisions decide
+      bx = slab<T, false>(lo.x, hi.x, tr.o.x, tr.d.x, tr.inv.x, tr.tmin, tr.tbest);
+      by = slab<T, false>(lo.y, hi.y, tr.o.y, tr.d.y, tr.inv.y, tr.tmin, tr.tbest);
+      bz = slab<T, false>(lo.z, hi.z, tr.o.z, tr.d.z, tr.inv.z, tr.tmin, tr.tbest);
+    }
+  } else {
+    bx = slab<T, FAST>(lo.x, hi.x, tr.o.x, tr.d.x, tr.inv.x, tr.tmin, tr.tbest);
+    by = slab<T, FAST>(lo.y, hi.y, tr.o.y, tr.d.y, tr.inv.y, tr.tmin, tr.tbest);
+    bz = slab<T, FAST>(lo.z, hi.z, tr.o.z, tr.d.z, tr.inv.z, tr.tmin, tr.tbest);
+  }
   if (bx && by && bz) { tr.push(bitsOf(hi.w)); tr.cur = bitsOf(lo.w); }
   else tr.next();
 }
@@ -160,7 +194,7 @@ template <class T, bool FAST> RTB_D void travReframe(const DScene<T>& sc, Trav<T
   tr.o = mk<T>(xld<T>(tr, X_WORLD + 0), xld<T>(tr, X_WORLD + 1), xld<T>(tr, X_WORLD + 2));
   tr.d = mk<T>(xld<T>(tr, X_WORLD + 3), xld<T>(tr, X_WORLD + 4), xld<T>(tr, X_WORLD + 5));
   for (int i = 0; i < fd; ++i) applyXform<T>(sc, tr.xu(X_CHAIN + i), tr.o, tr.d);
-  setInv<T, FAST>(tr);
+  setInv<T, FAST>(sc, tr);
 }
 
 // the rare kinds: frames, markers, media, Unhittable
@@ -178,7 +212,7 @@ RTB_D void stepRare(const DScene<T>& sc, Trav<T>& tr, Rng& rng, Instr<INSTR>& in
     tr.xu(X_CHAIN + fd) = ref;
     tr.setFd(fd + 1);
     applyXform<T>(sc, ref, tr.o, tr.d);
-    setInv<T, FAST>(tr);
+    setInv<T, FAST>(sc, tr);
     tr.push(K_MARK_FRAME << 28);
     tr.cur = child;
   } else if (kind == K_MARK_FRAME) {

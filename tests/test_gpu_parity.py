@@ -267,3 +267,13 @@ def test_cornell_matches_reference_png(gpu):
         assert abs(rgb[..., ch].mean() - gold[..., ch].mean()) < 1.0, (ch, rgb[..., ch].mean(), gold[..., ch].mean())
     a = rgb.reshape(25, 5, 25, 5, 3).mean(axis=(1, 3)); b = gold.reshape(25, 5, 25, 5, 3).mean(axis=(1, 3))
     assert np.sqrt(np.mean((a - b) ** 2)) < 5.0
+
+
+def test_hoisted_reciprocal_division_is_ieee(gpu):
+    """The literal fp32 slab test divides by the three ray-direction components with a reciprocal refined once per ray
+    (rt_device.cuh divByRcp): it must return the IEEE-rounded quotient bit for bit wherever the kernels use it."""
+    import ctypes as C
+    checked, bad = C.c_uint64(0), C.c_uint64(0)
+    rc = gpu.core().rt_selftest_division(400_000_000, 12345, C.byref(checked), C.byref(bad))
+    assert rc == 0
+    assert checked.value > 200_000_000 and bad.value == 0, (checked.value, bad.value)

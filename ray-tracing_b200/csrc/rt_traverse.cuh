@@ -123,24 +123,22 @@ RTB_D void stepNode(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
   const uint32_t idx = tr.cur & 0x0fffffffu;
   ins.visit(tr.cur); ins.boxTest();
   const Q4<T> lo = ldq(sc.nodes + 2 * (size_t)idx), hi = ldq(sc.nodes + 2 * (size_t)idx + 1);
-  bool bx, by, bz;
+  bool pass;
   if constexpr (!FAST && sizeof(T) == 4) {
-    const uint32_t md = tr.flags >> F_MODE_SHIFT;
-    bool ok = true;
-    bx = slabMode(md & 3u, lo.x, hi.x, tr.o.x, tr.d.x, tr.inv.x, tr.tmin, tr.tbest, ok);
-    by = slabMode((md >> 2) & 3u, lo.y, hi.y, tr.o.y, tr.d.y, tr.inv.y, tr.tmin, tr.tbest, ok);
-    bz = slabMode((md >> 4) & 3u, lo.z, hi.z, tr.o.z, tr.d.z, tr.inv.z, tr.tmin, tr.tbest, ok);
-    if (!ok) {  // a quotient left the validated range of the hoisted reciprocal (e.g. an exact 0): the generic divisions decide
-      bx = slab<T, false>(lo.x, hi.x, tr.o.x, tr.d.x, tr.inv.x, tr.tmin, tr.tbest);
-      by = slab<T, false>(lo.y, hi.y, tr.o.y, tr.d.y, tr.inv.y, tr.tmin, tr.tbest);
-      bz = slab<T, false>(lo.z, hi.z, tr.o.z, tr.d.z, tr.inv.z, tr.tmin, tr.tbest);
-    }
+    bool ok = (tr.flags & F_MODE_GENERIC) == 0u;  // no axis in the generic division mode
+    const bool bx = slabHoisted(lo.x, hi.x, tr.o.x, tr.d.x, tr.inv.x, tr.tmin, tr.tbest, ok);
+    const bool by = slabHoisted(lo.y, hi.y, tr.o.y, tr.d.y, tr.inv.y, tr.tmin, tr.tbest, ok);
+    const bool bz = slabHoisted(lo.z, hi.z, tr.o.z, tr.d.z, tr.inv.z, tr.tmin, tr.tbest, ok);
+    pass = bx && by && bz;
+    // a quotient left the validated range of the hoisted reciprocal (e.g. an exact 0), or generic mode: the literal test decides
+    if (!ok) pass = boxLiteral(lo.x, lo.y, lo.z, hi.x, hi.y, hi.z, tr.o.x, tr.o.y, tr.o.z, tr.d.x, tr.d.y, tr.d.z, tr.tmin, tr.tbest);
   } else {
-    bx = slab<T, FAST>(lo.x, hi.x, tr.o.x, tr.d.x, tr.inv.x, tr.tmin, tr.tbest);
-    by = slab<T, FAST>(lo.y, hi.y, tr.o.y, tr.d.y, tr.inv.y, tr.tmin, tr.tbest);
-    bz = slab<T, FAST>(lo.z, hi.z, tr.o.z, tr.d.z, tr.inv.z, tr.tmin, tr.tbest);
+    const bool bx = slab<T, FAST>(lo.x, hi.x, tr.o.x, tr.d.x, tr.inv.x, tr.tmin, tr.tbest);
+    const bool by = slab<T, FAST>(lo.y, hi.y, tr.o.y, tr.d.y, tr.inv.y, tr.tmin, tr.tbest);
+    const bool bz = slab<T, FAST>(lo.z, hi.z, tr.o.z, tr.d.z, tr.inv.z, tr.tmin, tr.tbest);
+    pass = bx && by && bz;
   }
-  if (bx && by && bz) { tr.push(bitsOf(hi.w)); tr.cur = bitsOf(lo.w); }
+  if (pass) { tr.push(bitsOf(hi.w)); tr.cur = bitsOf(lo.w); }
   else tr.next();
 }
 

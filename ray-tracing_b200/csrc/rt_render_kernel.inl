@@ -49,13 +49,14 @@ __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, Path
     evalHit<T>(sc, tr.o, tr.d, ps.time, tr.tbest, tr.bprim, tr.baux(), tr.bdepth(), &tr.xu(X_BCHAIN), tr.stride * (uint32_t)(sizeof(T) / 4), rec);
     const Q4<T> m = ldq(sc.mats + rec.mat);
     const uint32_t mkind = bitsOf(m.x), tex = bitsOf(m.y);
+    // the material's texture, evaluated at ONE call site (textureValue draws no random numbers, so its position relative to the
+    // samplers below is free): not needed by Dielectric (white) and by a light seen from its front face (black)
+    V3<T> tv = mk<T>(0, 0, 0);
+    if (mkind != M_DIELECTRIC && !(mkind == M_LIGHT && rec.front)) tv = textureValue<T, INSTR>(sc, tex, rec.u, rec.v, rec.p, ins);
     if (mkind == M_LIGHT) {  // scatter = Nothing -> emitted, back face only (Lib.hs:860, 880-885)
-      V3<T> e = mk<T>(0, 0, 0);
-      if (!rec.front) e = textureValue<T, INSTR>(sc, tex, rec.u, rec.v, rec.p, ins);
-      accAdd<T>(tr, ps.beta * e); ps.phase = PH_IDLE;
+      accAdd<T>(tr, ps.beta * tv); ps.phase = PH_IDLE;
       return false;
     } else if (mkind == M_LAMBERTIAN) {  // Lib.hs:823-836 with pdfGenerate/pdfValue of the mixture (367-382)
-      const V3<T> att = textureValue<T, INSTR>(sc, tex, rec.u, rec.v, rec.p, ins);
       const Onb<T> uvw = onbFromW(rec.n);
       const T rd = rnd<T>(ps.rng);
       V3<T> pdfD;
@@ -66,7 +67,7 @@ __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, Path
       const T v2 = (cosine <= 0) ? (T)0 : cosine / kPi<T>();
       const T c2 = dot(rec.n, dir);  // scatteringPdf (Lib.hs:874-878)
       const T spdf = (c2 < 0) ? (T)0 : c2 / kPi<T>();
-      ps.beta = ps.beta * att;
+      ps.beta = ps.beta * tv;
       qo = rec.p; qd = dir;
       if ((sc.lights_root >> 28) == K_UNHITTABLE) {  // htblPdfValue Unhittable = 0 without any traversal (Lib.hs:677-680, 1109)
         ins.count(13); ins.visit(sc.lights_root);
@@ -82,7 +83,7 @@ __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, Path
     } else if (mkind == M_METAL) {  // Lib.hs:837-841: never absorbs, fuzz unclamped
       const V3<T> rUnit = randomUnitVector<T>(ps.rng);
       const V3<T> reflected = reflectV(unit(tr.d), rec.n);
-      ps.beta = ps.beta * textureValue<T, INSTR>(sc, tex, rec.u, rec.v, rec.p, ins);
+      ps.beta = ps.beta * tv;
       qo = rec.p; qd = reflected + scale(m.z, rUnit);
       scattered = true;
     } else if (mkind == M_DIELECTRIC) {  // Lib.hs:842-859: xi is always drawn
@@ -97,10 +98,9 @@ __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, Path
       scattered = true;
     } else {  // Isotropic (Lib.hs:861-865) weighted by the generic scatteringPdf / 1.0 (867-878, 1329-1333)
       const V3<T> randDr = randomInUnitSphere<T>(ps.rng);
-      const V3<T> att = textureValue<T, INSTR>(sc, tex, rec.u, rec.v, rec.p, ins);
       const T c2 = dot(rec.n, randDr);
       const T spdf = (c2 < 0) ? (T)0 : c2 / kPi<T>();
-      ps.beta = scale(spdf / (T)1.0, ps.beta * att);
+      ps.beta = scale(spdf / (T)1.0, ps.beta * tv);
       qo = rec.p; qd = randDr;
       scattered = true;
     }

@@ -15,7 +15,7 @@
 namespace rtb {
 
 
-template <class T> struct MinBlocks { static constexpr int v = 4; };
+template <class T> struct MinBlocks { static constexpr int v = 6; };
 template <> struct MinBlocks<double> { static constexpr int v = 1; };
 
 #include "rt_render_kernel.inl"

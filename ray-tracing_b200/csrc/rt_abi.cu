@@ -277,9 +277,9 @@ int renderLaunch(SceneEntry* e, const RtRenderParams& q, double* d_out, cudaStre
   // chunk: whole pixels where possible, ~1024 paths, at least 16 chunks per resident warp slot for balance
   unsigned long long warps = (unsigned long long)e->numSMs * 16ull;
   unsigned long long chunk = 1024;
-  while (chunk > 64 && a.total_paths / chunk < warps * 8ull) chunk /= 2;
+  while (chunk > 32 && a.total_paths / chunk < warps * 8ull) chunk /= 2;
   a.chunk = (uint32_t)chunk;
-  a.shadeMin = tuneParam("RTB_SHADE_MIN", 8); a.keepNode = std::max(1u, tuneParam("RTB_KEEP_NODE", 12)); a.keepLeaf = std::max(1u, tuneParam("RTB_KEEP_LEAF", 8));
+  a.shadeMin = tuneParam("RTB_SHADE_MIN", 16); a.keepNode = std::max(1u, tuneParam("RTB_KEEP_NODE", 12)); a.keepLeaf = std::max(1u, tuneParam("RTB_KEEP_LEAF", 8));
   a.counter = e->d_counter; a.ctr = counted ? e->d_counter + 1 : nullptr; a.out = d_out;
   cudaError_t ce = (q.flags & RT_FLAG_FAST_MATH) ? launchRender<true>((int)q.precision, counted ? 1 : 0, dsc, a, e->hs.stackDepth, e->numSMs, st, gridOut)
                                                  : launchRender<false>((int)q.precision, counted ? 1 : 0, dsc, a, e->hs.stackDepth, e->numSMs, st, gridOut);

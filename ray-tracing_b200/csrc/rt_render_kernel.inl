@@ -43,7 +43,7 @@ template <class T, int INSTR>
 __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, PathState<T>& ps, Instr<INSTR>& ins, V3<T>& qo, V3<T>& qd) {
   bool scattered = false;  // the path continues with (qo, qd) as the next bounce ray
   qo = tr.o; qd = tr.d;    // all frames are closed when a query ends: this is the query's world ray
-  if (ps.phase == PH_MAIN) {
+  {
     if (!tr.qhit()) { accAdd<T>(tr, ps.beta * mk<T>(sc.bg[0], sc.bg[1], sc.bg[2])); ps.phase = PH_IDLE; return false; }  // Lib.hs:1310-1313
     HitRec<T> rec;
     evalHit<T>(sc, tr.o, tr.d, ps.time, tr.tbest, tr.bprim, tr.baux(), tr.bdepth(), &tr.xu(X_BCHAIN), tr.stride * (uint32_t)(sizeof(T) / 4), rec);
@@ -104,40 +104,6 @@ __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, Path
       qo = rec.p; qd = randDr;
       scattered = true;
     }
-  } else {  // PH_LPDF: htblPdfValue (Lib.hs:673-705) for the light in X_CURLIGHT, walked depth-first, left first
-    const uint32_t curLight = tr.xu(X_CURLIGHT);
-    const T curW = xld<T>(tr, X_CURW);
-    uint32_t lsp = tr.xu(X_LSP);
-    if (tr.qhit()) {
-      const uint32_t lk = curLight >> 28, li = curLight & 0x0fffffffu;
-      if (lk == K_RECT_XZ) {
-        const Q4<T> ra = ldq(sc.rects + 2 * (size_t)li);
-        const T area = (ra.y - ra.x) * (ra.w - ra.z);
-        const T distanceSquared = tr.tbest * tr.tbest * sqlen(tr.d);
-        const T cosine = mabs(tr.d.y / len(tr.d));  // |v . (0,+-1,0)| / |v|
-        xst<T>(tr, X_LV1, xld<T>(tr, X_LV1) + curW * (distanceSquared / (cosine * area)));
-      } else if (lk == K_SPHERE) {
-        const Q4<T> q = ldq(sc.spheres + li);
-        const T cosThetaMax = msqrt(1 - q.w * q.w / sqlen(mk<T>(q.x, q.y, q.z) - tr.o));
-        const T solidAngle = 2 * kPi<T>() * (1 - cosThetaMax);
-        xst<T>(tr, X_LV1, xld<T>(tr, X_LV1) + curW * (1 / solidAngle));
-      } else if (lk == K_BVH) {
-        const uint4 sz = __ldg(sc.node_sz + li);
-        const uint32_t lc = bitsOf(ldq(sc.nodes + 2 * (size_t)li).w), rc = bitsOf(ldq(sc.nodes + 2 * (size_t)li + 1).w);
-        if (lsp + 2 <= (uint32_t)kMaxLightDepth) {
-          tr.xu(X_LREF + (int)lsp) = rc; xst<T>(tr, X_LWT + (int)lsp, curW * ((T)sz.z / (T)sz.x)); ++lsp;
-          tr.xu(X_LREF + (int)lsp) = lc; xst<T>(tr, X_LWT + (int)lsp, curW * ((T)sz.y / (T)sz.x)); ++lsp;
-        }
-      }
-    }
-    if (lsp > 0) {
-      --lsp;
-      tr.xu(X_CURLIGHT) = tr.xu(X_LREF + (int)lsp); xst<T>(tr, X_CURW, xld<T>(tr, X_LWT + (int)lsp)); tr.xu(X_LSP) = lsp;
-      return true;
-    }
-    const T pdfVal = (T)0.5 * (xld<T>(tr, X_LV1) + xld<T>(tr, X_LV2));
-    ps.beta = scale(xld<T>(tr, X_LSPDF) / pdfVal, ps.beta);
-    ps.phase = PH_MAIN; scattered = true;
   }
   if (scattered) {  // rayColorHelp newRay (d - 1) (Lib.hs:1321-1333)
     --ps.depthLeft;
@@ -145,6 +111,56 @@ __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, Path
     return true;
   }
   return false;
+}
+
+// A finished query of the Lambertian mixture pdf's light term, htblPdfValue (Lib.hs:673-705): account the light in X_CURLIGHT
+// (walked depth-first, left first), then start the query of the next light on the same ray, or — all lights done — weight the
+// throughput (Lib.hs:1329-1333) and start the bounce's `hit world`.  Runs right after the traversal step that finished the query
+// (not through the shade class): the lane stays in the traversal classes.
+template <class T, int INSTR, bool FAST>
+RTB_D void lpdfAdvance(const DScene<T>& sc, Trav<T>& tr, PathState<T>& ps, Instr<INSTR>& ins) {
+  const uint32_t curLight = tr.xu(X_CURLIGHT);
+  const T curW = xld<T>(tr, X_CURW);
+  uint32_t lsp = tr.xu(X_LSP);
+  if (tr.qhit()) {
+    const uint32_t lk = curLight >> 28, li = curLight & 0x0fffffffu;
+    if (lk == K_RECT_XZ) {
+      const Q4<T> ra = ldq(sc.rects + 2 * (size_t)li);
+      const T area = (ra.y - ra.x) * (ra.w - ra.z);
+      const T distanceSquared = tr.tbest * tr.tbest * sqlen(tr.d);
+      const T cosine = mabs(tr.d.y / len(tr.d));  // |v . (0,+-1,0)| / |v|
+      xst<T>(tr, X_LV1, xld<T>(tr, X_LV1) + curW * (distanceSquared / (cosine * area)));
+    } else if (lk == K_SPHERE) {
+      const Q4<T> q = ldq(sc.spheres + li);
+      const T cosThetaMax = msqrt(1 - q.w * q.w / sqlen(mk<T>(q.x, q.y, q.z) - tr.o));
+      const T solidAngle = 2 * kPi<T>() * (1 - cosThetaMax);
+      xst<T>(tr, X_LV1, xld<T>(tr, X_LV1) + curW * (1 / solidAngle));
+    } else if (lk == K_BVH) {
+      const uint4 sz = __ldg(sc.node_sz + li);
+      const uint32_t lc = bitsOf(ldq(sc.nodes + 2 * (size_t)li).w), rc = bitsOf(ldq(sc.nodes + 2 * (size_t)li + 1).w);
+      if (lsp + 2 <= (uint32_t)kMaxLightDepth) {
+        tr.xu(X_LREF + (int)lsp) = rc; xst<T>(tr, X_LWT + (int)lsp, curW * ((T)sz.z / (T)sz.x)); ++lsp;
+        tr.xu(X_LREF + (int)lsp) = lc; xst<T>(tr, X_LWT + (int)lsp, curW * ((T)sz.y / (T)sz.x)); ++lsp;
+      }
+    }
+  }
+  const V3<T> qo = tr.o, qd = tr.d;  // all frames are closed: the query's world ray = the scattered ray
+  uint32_t root;
+  if (lsp > 0) {
+    --lsp;
+    root = tr.xu(X_LREF + (int)lsp);
+    tr.xu(X_CURLIGHT) = root; xst<T>(tr, X_CURW, xld<T>(tr, X_LWT + (int)lsp)); tr.xu(X_LSP) = lsp;
+  } else {
+    const T pdfVal = (T)0.5 * (xld<T>(tr, X_LV1) + xld<T>(tr, X_LV2));
+    ps.beta = scale(xld<T>(tr, X_LSPDF) / pdfVal, ps.beta);
+    ps.phase = PH_MAIN;
+    --ps.depthLeft;  // rayColorHelp newRay (d - 1) (Lib.hs:1321-1333)
+    if (ps.depthLeft <= 0) { accAdd<T>(tr, ps.beta * mk<T>(0, 0, 0)); ps.phase = PH_IDLE; return; }  // cur stays kEmpty: regenerated by the shade class
+    root = sc.world_root;
+    ins.count(1);
+  }
+  ins.count(13);
+  travBegin<T, FAST>(sc, tr, root, qo, qd, kEps<T>(), kInf<T>());
 }
 
 template <class T, class S, int INSTR, bool FAST>
@@ -201,6 +217,9 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
       if (cls == 2) stepRect<T, INSTR>(sc, tr, ins);
     } else if (pick == 3) {
       if (cls == 3) stepRare<T, INSTR, FAST>(sc, tr, ps.rng, ins);
+    }
+    if (pick != 4) {
+      if (ps.phase == PH_LPDF && tr.cur == kEmpty) lpdfAdvance<T, INSTR, FAST>(sc, tr, ps, ins);
     } else {
       // ---- shade class: (1) consume finished queries
       bool start = false; V3<T> qo = tr.o, qd = tr.d;

@@ -168,6 +168,9 @@ typedef struct RtStats {
   uint64_t samples;        /* camera paths traced by this call */
   uint64_t launches;       /* kernels launched by this call */
   uint64_t counters[16];   /* RT_CTR_* when the call was made with counters enabled, else 0 */
+  uint64_t sched[16];      /* warp-scheduler statistics of the instrumented kernel: [0..4] iterations that ran class c (node, sphere,
+                              rect, rare, shade), [5..9] lanes served by them, [10..14] lanes waiting per class summed over all
+                              iterations, [15] iterations */
 } RtStats;
 /* counters (algorithmic work, same definitions as the oracle's): */
 enum RtCounter { RT_CTR_PATHS = 0, RT_CTR_BOUNCES = 1, RT_CTR_BOX_TESTS = 2, RT_CTR_SPHERE_TESTS = 3, RT_CTR_MOVING_TESTS = 4,

@@ -56,7 +56,7 @@ class RtRenderParams(C.Structure):
 
 class RtStats(C.Structure):
     _fields_ = [("kernel_ms", C.c_double), ("h2d_ms", C.c_double), ("d2h_ms", C.c_double), ("samples", C.c_uint64),
-                ("launches", C.c_uint64), ("counters", C.c_uint64 * 16)]
+                ("launches", C.c_uint64), ("counters", C.c_uint64 * 16), ("sched", C.c_uint64 * 16)]
 
 
 class RtLimits(C.Structure):
@@ -82,7 +82,7 @@ def core():
     """librt_b200.so.  Raises if it has not been built: there is no other implementation to fall back to."""
     global _core
     if _core is None:
-        path = os.path.join(_HERE, "librt_b200.so")
+        path = os.path.join(_HERE, os.environ.get("RTB_CORE_LIB", "librt_b200.so"))  # override: A/B builds in tools/ only
         if not os.path.exists(path):
             raise RuntimeError("librt_b200.so is missing: run __graft_entry__.build() (no CPU fallback exists)")
         L = C.CDLL(path, mode=C.RTLD_GLOBAL)

@@ -117,6 +117,7 @@ class DeviceScene:
         stats = dict(kernel_ms=st.kernel_ms, d2h_ms=st.d2h_ms, samples=int(st.samples), launches=int(st.launches))
         if counted:
             stats["counters"] = dict(zip(COUNTER_NAMES, (int(x) for x in st.counters)))
+            stats["sched"] = [int(x) for x in st.sched]
         return out, stats
 
     def render_device(self, d_ptr, W, H, spp, stream=0, timed=False, **kw):

@@ -55,7 +55,7 @@ struct SceneEntry {
   int device = 0, numSMs = 148;
   DevBuffers<float> f32;
   DevBuffers<double> f64;
-  unsigned long long* d_counter = nullptr;  // [0] path counter, [1..16] work counters
+  unsigned long long* d_counter = nullptr;  // [0] path counter, [1..16] work counters, [17..32] scheduler statistics
   double* d_fb = nullptr; size_t fbElems = 0;
   double* h_fb = nullptr; size_t hfbElems = 0;  // pinned staging
   ~SceneEntry() {
@@ -266,8 +266,8 @@ int renderLaunch(SceneEntry* e, const RtRenderParams& q, double* d_out, cudaStre
   const void* dsc = nullptr;
   int rc = deviceScene(e, q.precision, &dsc);
   if (rc) return rc;
-  if (!e->d_counter) { CU(cudaMalloc(&e->d_counter, 17 * sizeof(unsigned long long))); }
-  CU(cudaMemsetAsync(e->d_counter, 0, 17 * sizeof(unsigned long long), st));
+  if (!e->d_counter) { CU(cudaMalloc(&e->d_counter, 33 * sizeof(unsigned long long))); }
+  CU(cudaMemsetAsync(e->d_counter, 0, 33 * sizeof(unsigned long long), st));
   if (q.sample_count == 0) return RT_OK;
   RenderArgs a{};
   a.W = q.width; a.H = q.height; a.s0 = q.sample_offset; a.ns = q.sample_count; a.maxDepth = q.max_depth;
@@ -279,7 +279,14 @@ int renderLaunch(SceneEntry* e, const RtRenderParams& q, double* d_out, cudaStre
   unsigned long long chunk = 1024;
   while (chunk > 32 && a.total_paths / chunk < warps * 8ull) chunk /= 2;
   a.chunk = (uint32_t)chunk;
-  a.shadeMin = tuneParam("RTB_SHADE_MIN", 16); a.keepNode = std::max(1u, tuneParam("RTB_KEEP_NODE", 12)); a.keepLeaf = std::max(1u, tuneParam("RTB_KEEP_LEAF", 8));
+  // scheduler thresholds (rt_render_kernel.inl): single rects are cheap steps and worth running for 3 lanes, cuboid-heavy scenes batch
+  // 6; media make the rare class frequent (3 rare steps per medium visit) and worth running for 4 lanes.  Measured on the
+  // reference scenes (tools/knob_sweep.py); results never depend on these.
+  const HostScene& hs = e->hs;
+  a.shadeMin = tuneParam("RTB_SHADE_MIN", 16);
+  a.rectMin = std::max(1u, tuneParam("RTB_RECT_MIN", hs.n_cuboids > hs.n_rects ? 6u : 3u));
+  a.rareMin = std::max(1u, tuneParam("RTB_RARE_MIN", hs.n_media > 0 ? 4u : 8u));
+  a.keepNode = std::max(1u, tuneParam("RTB_KEEP_NODE", 12)); a.keepLeaf = std::max(1u, tuneParam("RTB_KEEP_LEAF", 8));
   a.counter = e->d_counter; a.ctr = counted ? e->d_counter + 1 : nullptr; a.out = d_out;
   cudaError_t ce = (q.flags & RT_FLAG_FAST_MATH) ? launchRender<true>((int)q.precision, counted ? 1 : 0, dsc, a, e->hs.stackDepth, e->numSMs, st, gridOut)
                                                  : launchRender<false>((int)q.precision, counted ? 1 : 0, dsc, a, e->hs.stackDepth, e->numSMs, st, gridOut);
@@ -331,9 +338,9 @@ int renderHost(rt_scene_t scene, const RtRenderParams* params, double* out, RtSt
     stats->samples = (uint64_t)(q.row1 - q.row0) * (q.col1 - q.col0) * q.sample_count;
     stats->launches = q.sample_count ? 1 : 0;
     if (counted) {
-      unsigned long long c[17];
+      unsigned long long c[33];
       CU(cudaMemcpy(c, e->d_counter, sizeof(c), cudaMemcpyDeviceToHost));
-      for (int i = 0; i < 16; ++i) stats->counters[i] = c[i + 1];
+      for (int i = 0; i < 16; ++i) { stats->counters[i] = c[i + 1]; stats->sched[i] = c[i + 17]; }
     }
   }
   cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);

@@ -183,11 +183,14 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
   if (lane == 0) { ws[0] = 0; ws[1] = 0; ws[2] = 0; ws[3] = 0; }
   __syncwarp();
   bool exhausted = false;
+  unsigned long long sch[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // INSTR == 1 only
   const uint32_t regionW = a.col1 - a.col0;
 
   for (;;) {
     // ---- fast votes: a node step when at least keepNode lanes wait for one, else a sphere step when keepLeaf lanes do;
-    //      otherwise the full vote: the class most lanes wait for, shade as soon as shadeMin lanes wait for it
+    //      otherwise the full vote: the class most lanes wait for, but rare steps as soon as rareMin lanes wait for one, rect /
+    //      cuboid steps from rectMin and shade from shadeMin (lanes parked in a minority class are lanes the majority classes
+    //      run without; the thresholds are tuned per scene family)
     const uint32_t kind = tr.cur >> 28;
     const bool isNode = kind == K_BVH, isLeaf = kind == K_SPHERE || kind == K_MOVING;
     const int cls = stepClass(tr.cur);
@@ -203,12 +206,20 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
         int best = cN;
         pick = 0;
         if (cL > best) { pick = 1; best = cL; }
-        if (c2 > best) { pick = 2; best = c2; }
-        if (c3 > best) { pick = 3; best = c3; }
-        if (c4 > best || c4 >= (int)a.shadeMin) pick = 4;
+        if (c4 > best || c4 >= (int)a.shadeMin) { pick = 4; best = 32; }
+        if (c2 > best || c2 >= (int)a.rectMin) { pick = 2; best = 32; }
+        if (c3 > best || c3 >= (int)a.rareMin) pick = 3;
       }
     }
 
+    if constexpr (INSTR == 1) {  // scheduler statistics (RtStats::sched)
+      const int n0 = __popc(__ballot_sync(0xffffffffu, cls == 0)), n1 = __popc(__ballot_sync(0xffffffffu, cls == 1)), n2 = __popc(__ballot_sync(0xffffffffu, cls == 2)),
+                n3 = __popc(__ballot_sync(0xffffffffu, cls == 3)), n4 = __popc(__ballot_sync(0xffffffffu, cls == 4));
+      if (lane == 0) {
+        const int served = pick == 0 ? n0 : pick == 1 ? n1 : pick == 2 ? n2 : pick == 3 ? n3 : n4;
+        ++sch[pick]; sch[5 + pick] += (unsigned)served; sch[10] += n0; sch[11] += n1; sch[12] += n2; sch[13] += n3; sch[14] += n4; ++sch[15];
+      }
+    }
     if (pick == 0) {
       if (isNode) stepNode<T, INSTR, FAST>(sc, tr, ins);
     } else if (pick == 1) {
@@ -288,6 +299,7 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
   accFlush<T>(tr, a.out);
   if constexpr (INSTR == 1) {
     for (int i = 0; i < 16; ++i) if (ins.c[i]) atomicAdd(a.ctr + i, (unsigned long long)ins.c[i]);
+    if (lane == 0) for (int i = 0; i < 16; ++i) if (sch[i]) atomicAdd(a.ctr + 16 + i, sch[i]);
   }
 }
 

@@ -104,7 +104,7 @@ def run_reference(args, W, H, rank):
     earth = pkg.load_earth() if args.scene in ("earth", "random", "next_week_final") else None
     osc = O.OracleScene(args.scene, earth=earth, synth_n=args.synth_n)
     cores = os.cpu_count() or 1
-    spp = args.ref_spp if args.scene != "synthetic" else 1
+    spp = (args.ref_spp or 32) if args.scene != "synthetic" else 1
     w, h = (W, H) if args.scene != "synthetic" else (48, 27)
     times = []
     for i in range(args.warmup + args.steps):
@@ -132,7 +132,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--scene", default="random", choices=list(SCENE_DOC))
     ap.add_argument("--spp", type=int, default=0)
-    ap.add_argument("--ref-spp", type=int, default=8)
+    ap.add_argument("--ref-spp", type=int, default=0, help="spp of the CPU sample (default: 100 for the cpu_baseline leg = perflogs.org:1, 32 per step for --impl reference)")
     ap.add_argument("--synth-n", type=int, default=1000)
     ap.add_argument("--fast", action="store_true", help="RT_FLAG_FAST_MATH kernels (not bit-exact; reported separately)")
     ap.add_argument("--precision", type=int, default=0)
@@ -270,11 +270,12 @@ def main():
             osc = O.OracleScene(args.scene, earth=earth, synth_n=args.synth_n)
             cores = os.cpu_count() or 1
             w, h = (W, H) if args.scene != "synthetic" else (48, 27)
+            ref_spp = 1 if args.scene == "synthetic" else (args.ref_spp or {"random": 100, "random_book1": 100, "cornell": 100, "next_week_final": 16}[args.scene])
             t0 = time.time()
-            osc.render(w, h, args.ref_spp if args.scene != "synthetic" else 1, depth=50, prec=O.PREC_F64, mode=0, seed=4242, threads=cores)
+            osc.render(w, h, ref_spp, depth=50, prec=O.PREC_F64, mode=0, seed=4242, threads=cores)
             dt = time.time() - t0
-            line["cpu_baseline"] = {"value": w * h * (args.ref_spp if args.scene != "synthetic" else 1) / dt, "unit": "samples/s", "cores": cores, "kind": "port",
-                                    "sample": "%dx%d at %d spp, depth 50, oracle<double> in runRender's RNG plumbing, %d threads (%.1f s)" % (w, h, args.ref_spp if args.scene != "synthetic" else 1, cores, dt)}
+            line["cpu_baseline"] = {"value": w * h * ref_spp / dt, "unit": "samples/s", "cores": cores, "kind": "port",
+                                    "sample": "%dx%d at %d spp, depth 50, oracle<double> in runRender's RNG plumbing, %d threads (%.1f s)" % (w, h, ref_spp, cores, dt)}
         print(json.dumps(line))
     ds.destroy()
     if world > 1:

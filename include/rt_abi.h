@@ -37,7 +37,7 @@ extern "C" {
 
 /* Hittable reference = (kind << 28) | index-within-kind.  Kinds follow the constructors of
  * `data Hittable` (Lib.hs:521-585) with `Rect` split by its Rectangle constructor (Lib.hs:607-647); the three rect
- * kinds index one shared rect array. */
+ * kinds index one shared rect array.  Every array may hold at most 2^27 entries (rt_scene_create rejects more). */
 enum RtHittableKind {
   RT_UNHITTABLE = 0,
   RT_SPHERE = 1,

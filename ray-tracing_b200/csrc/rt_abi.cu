@@ -75,7 +75,7 @@ template <class V, class P> void copyIn(V& dst, const P* src, size_t n) {
 }
 
 bool refOk(const HostScene& h, uint32_t ref) {
-  uint32_t k = ref >> 28, i = ref & 0x0fffffffu;
+  uint32_t k = ref >> 28, i = ref & 0x0fffffffu;  // full 28-bit field: counts are limited to 27 bits, so a set bit 27 is out of range
   switch (k) {
     case K_UNHITTABLE: return true;
     case K_SPHERE: return i < h.n_spheres;
@@ -104,7 +104,7 @@ struct Analysis {
     if (st == 2) return;
     if (st == 1) { cycle = true; return; }
     st = 1;
-    uint32_t k = ref >> 28, i = ref & 0x0fffffffu;
+    uint32_t k = ref >> 28, i = ref & kIdxMask;
     int sn = 0, fr = 0, md = 0, sz = 1;
     if (k == K_BVH) {
       uint32_t l = h.node_left[i], r = h.node_right[i];
@@ -132,7 +132,7 @@ struct Analysis {
 int lightDepth(const HostScene& h, uint32_t ref, int d = 0) {
   if (d > 64) return d;
   if ((ref >> 28) != K_BVH) return 1;
-  uint32_t i = ref & 0x0fffffffu;
+  uint32_t i = ref & kIdxMask;
   return 1 + std::max(lightDepth(h, h.node_left[i], d + 1), lightDepth(h, h.node_right[i], d + 1));
 }
 
@@ -151,6 +151,13 @@ template <class T, class V> int upload(DevBuffers<T>& db, const std::vector<V>& 
   return RT_OK;
 }
 
+// which leaf classes are tested as pairs (bit 0 sphere-like, bit 1 rect / cuboid): sphere pairs always pay; rect / cuboid pairs pay
+// in cuboid-heavy scenes (cfg3 +3 %) and cost in rect scenes (cfg4 -9 %).  RTB_PAIR overrides for experiments.
+static int pairMask(const HostScene& h) {
+  const char* v = std::getenv("RTB_PAIR");
+  return v ? std::atoi(v) : (h.n_cuboids > h.n_rects ? 3 : 1);
+}
+
 // pack the flattened scene into the device layout (rt_device.cuh DScene<T>); doubles are rounded to T here
 template <class T> int buildDevice(const HostScene& h, DevBuffers<T>& db) {
   if (db.ready) return RT_OK;
@@ -160,9 +167,14 @@ template <class T> int buildDevice(const HostScene& h, DevBuffers<T>& db) {
       translates(h.n_translates), rotates(h.n_rotates), media(h.n_media), mats(h.n_materials), texs(2 * (size_t)h.n_textures), pvec(256 * (size_t)h.n_perlin);
   std::vector<uint4> nsz(h.n_nodes);
   std::vector<uint8_t> pperm(768 * (size_t)h.n_perlin);
+  const int pmask = pairMask(h);
   for (size_t i = 0; i < h.n_nodes; ++i) {
     const double* b = &h.node_box[i * 6];
-    nodes[2 * i] = Q{(T)b[0], (T)b[1], (T)b[2], B(h.node_left[i])};
+    // both children leaves of one step class (sphere-like, or rect / cuboid): mark the pair (rt_device.cuh kPairBit)
+    auto leafClass = [](uint32_t r) { uint32_t k = r >> 28; return (k == K_SPHERE || k == K_MOVING) ? 1 : ((k >= K_RECT_XY && k <= K_CUBOID) ? 2 : 0); };
+    const int lcl = leafClass(h.node_left[i]);
+    const uint32_t pair = (lcl != 0 && ((pmask >> (lcl - 1)) & 1) && lcl == leafClass(h.node_right[i])) ? kPairBit : 0u;
+    nodes[2 * i] = Q{(T)b[0], (T)b[1], (T)b[2], B(h.node_left[i] | pair)};
     nodes[2 * i + 1] = Q{(T)b[3], (T)b[4], (T)b[5], B(h.node_right[i])};
     nsz[i] = make_uint4(h.node_size[i], h.node_lsize[i], h.node_rsize[i], 0);
   }
@@ -378,7 +390,7 @@ int rt_scene_create(const RtSceneDesc* d, int device, rt_scene_t* out) {
       !need(d->n_textures, d->tex_b) || !need(d->n_textures, d->tex_scale) || !need(d->n_perlin, d->perlin_ranvec) || !need(d->n_perlin, d->perlin_perm) ||
       !need(d->n_images, d->image_rgb) || !need(d->n_images, d->image_w) || !need(d->n_images, d->image_h))
     return fail(RT_ERR_ARG, "a non-empty array is null");
-  const uint32_t lim = 0x0fffffffu;
+  const uint32_t lim = kIdxMask;  // 27-bit indices: bit 27 of a ref is the pair mark
   if (d->n_nodes > lim || d->n_spheres > lim || d->n_moving > lim || d->n_rects > lim || d->n_cuboids > lim) return fail(RT_ERR_ARG, "too many objects");
 
   auto e = std::make_unique<SceneEntry>();

@@ -123,7 +123,7 @@ RTB_D void lpdfAdvance(const DScene<T>& sc, Trav<T>& tr, PathState<T>& ps, Instr
   const T curW = xld<T>(tr, X_CURW);
   uint32_t lsp = tr.xu(X_LSP);
   if (tr.qhit()) {
-    const uint32_t lk = curLight >> 28, li = curLight & 0x0fffffffu;
+    const uint32_t lk = curLight >> 28, li = curLight & kIdxMask;
     if (lk == K_RECT_XZ) {
       const Q4<T> ra = ldq(sc.rects + 2 * (size_t)li);
       const T area = (ra.y - ra.x) * (ra.w - ra.z);
@@ -137,7 +137,7 @@ RTB_D void lpdfAdvance(const DScene<T>& sc, Trav<T>& tr, PathState<T>& ps, Instr
       xst<T>(tr, X_LV1, xld<T>(tr, X_LV1) + curW * (1 / solidAngle));
     } else if (lk == K_BVH) {
       const uint4 sz = __ldg(sc.node_sz + li);
-      const uint32_t lc = bitsOf(ldq(sc.nodes + 2 * (size_t)li).w), rc = bitsOf(ldq(sc.nodes + 2 * (size_t)li + 1).w);
+      const uint32_t lc = bitsOf(ldq(sc.nodes + 2 * (size_t)li).w) & ~kPairBit, rc = bitsOf(ldq(sc.nodes + 2 * (size_t)li + 1).w);
       if (lsp + 2 <= (uint32_t)kMaxLightDepth) {
         tr.xu(X_LREF + (int)lsp) = rc; xst<T>(tr, X_LWT + (int)lsp, curW * ((T)sz.z / (T)sz.x)); ++lsp;
         tr.xu(X_LREF + (int)lsp) = lc; xst<T>(tr, X_LWT + (int)lsp, curW * ((T)sz.y / (T)sz.x)); ++lsp;

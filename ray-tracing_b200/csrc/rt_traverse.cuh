@@ -120,7 +120,7 @@ template <class T> RTB_D void travAccept(Trav<T>& tr, T t, uint32_t ref, uint32_
 
 template <class T, int INSTR, bool FAST>
 RTB_D void stepNode(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
-  const uint32_t idx = tr.cur & 0x0fffffffu;
+  const uint32_t idx = tr.cur & kIdxMask;
   ins.visit(tr.cur); ins.boxTest();
   const Q4<T> lo = ldq(sc.nodes + 2 * (size_t)idx), hi = ldq(sc.nodes + 2 * (size_t)idx + 1);
   bool pass;
@@ -138,50 +138,73 @@ RTB_D void stepNode(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
     const bool bz = slab<T, FAST>(lo.z, hi.z, tr.o.z, tr.d.z, tr.inv.z, tr.tmin, tr.tbest);
     pass = bx && by && bz;
   }
-  if (pass) { tr.push(bitsOf(hi.w)); tr.cur = bitsOf(lo.w); }
-  else tr.next();
+  if (pass) {
+    const uint32_t lc = bitsOf(lo.w);
+    if (lc & kPairBit) tr.cur = (lc & 0xf0000000u) | kPairBit | idx;  // both children are leaves of one class: one pair step, nothing stacked
+    else { tr.push(bitsOf(hi.w)); tr.cur = lc; }
+  } else tr.next();
 }
 
 template <class T, class S, int INSTR>
 RTB_D void stepSphere(const DScene<T>& sc, Trav<T>& tr, T time, Instr<INSTR>& ins) {
-  const uint32_t ref = tr.cur, idx = ref & 0x0fffffffu;
-  ins.visit(ref);
-  V3<T> ctr; T rad;
-  if ((ref >> 28) == K_SPHERE) {
-    const Q4<T> q = ldq(sc.spheres + idx);
-    ctr = mk<T>(q.x, q.y, q.z); rad = q.w;
-  } else {  // MovingSphere (Lib.hs:1106-1108)
-    const Q4<T> a = ldq(sc.moving + 3 * (size_t)idx), b = ldq(sc.moving + 3 * (size_t)idx + 1), c = ldq(sc.moving + 3 * (size_t)idx + 2);
-    const V3<T> c0 = mk<T>(a.x, a.y, a.z), c1 = mk<T>(b.x, b.y, b.z);
-    ctr = c0 + scale((time - b.w) / c.x, c1 - c0); rad = a.w;
+  uint32_t ref = tr.cur, ref2 = kNone;
+  if (ref & kPairBit) {  // the two leaves of a bottom node, left then right (Lib.hs:971-988)
+    const uint32_t n = ref & kIdxMask;
+    ref = bitsOf(ldq(sc.nodes + 2 * (size_t)n).w) & ~kPairBit; ref2 = bitsOf(ldq(sc.nodes + 2 * (size_t)n + 1).w);
   }
-  T t;
-  if (sphereT<T, S>(ctr, rad, tr.o, tr.d, tr.tmin, tr.tbest, t)) { ins.sphereHit(); travAccept<T>(tr, t, ref, 0); }
+#pragma unroll 1
+  for (;;) {
+    const uint32_t idx = ref & kIdxMask;
+    ins.visit(ref);
+    V3<T> ctr; T rad;
+    if ((ref >> 28) == K_SPHERE) {
+      const Q4<T> q = ldq(sc.spheres + idx);
+      ctr = mk<T>(q.x, q.y, q.z); rad = q.w;
+    } else {  // MovingSphere (Lib.hs:1106-1108)
+      const Q4<T> a = ldq(sc.moving + 3 * (size_t)idx), b = ldq(sc.moving + 3 * (size_t)idx + 1), c = ldq(sc.moving + 3 * (size_t)idx + 2);
+      const V3<T> c0 = mk<T>(a.x, a.y, a.z), c1 = mk<T>(b.x, b.y, b.z);
+      ctr = c0 + scale((time - b.w) / c.x, c1 - c0); rad = a.w;
+    }
+    T t;
+    if (sphereT<T, S>(ctr, rad, tr.o, tr.d, tr.tmin, tr.tbest, t)) { ins.sphereHit(); travAccept<T>(tr, t, ref, 0); }
+    if (ref2 == kNone) break;
+    ref = ref2; ref2 = kNone;
+  }
   tr.next();
 }
 
 // Rect and Cuboid leaves
 template <class T, int INSTR>
 RTB_D void stepRect(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
-  const uint32_t ref = tr.cur, kind = ref >> 28, idx = ref & 0x0fffffffu;
-  ins.visit(ref);
-  if (kind != K_CUBOID) {
-    const Q4<T> a = ldq(sc.rects + 2 * (size_t)idx), b = ldq(sc.rects + 2 * (size_t)idx + 1);
-    T t;
-    if (rectT<T>(kind - K_RECT_XY, a.x, a.y, a.z, a.w, b.x, tr.o, tr.d, tr.tmin, tr.tbest, t)) travAccept<T>(tr, t, ref, 0);
-  } else {  // Lib.hs:989-1004: foldr over the six rects => last first; strict `<` replaces
-    const Q4<T> mn = ldq(sc.cuboids + 2 * (size_t)idx), mx = ldq(sc.cuboids + 2 * (size_t)idx + 1);
-    bool acc = false; T tNew = 0; uint32_t aux = 0;
+  uint32_t ref = tr.cur, ref2 = kNone;
+  if (ref & kPairBit) {  // the two leaves of a bottom node, left then right
+    const uint32_t n = ref & kIdxMask;
+    ref = bitsOf(ldq(sc.nodes + 2 * (size_t)n).w) & ~kPairBit; ref2 = bitsOf(ldq(sc.nodes + 2 * (size_t)n + 1).w);
+  }
+#pragma unroll 1
+  for (;;) {
+    const uint32_t kind = ref >> 28, idx = ref & kIdxMask;
+    ins.visit(ref);
+    if (kind != K_CUBOID) {
+      const Q4<T> a = ldq(sc.rects + 2 * (size_t)idx), b = ldq(sc.rects + 2 * (size_t)idx + 1);
+      T t;
+      if (rectT<T>(kind - K_RECT_XY, a.x, a.y, a.z, a.w, b.x, tr.o, tr.d, tr.tmin, tr.tbest, t)) travAccept<T>(tr, t, ref, 0);
+    } else {  // Lib.hs:989-1004: foldr over the six rects => last first; strict `<` replaces
+      const Q4<T> mn = ldq(sc.cuboids + 2 * (size_t)idx), mx = ldq(sc.cuboids + 2 * (size_t)idx + 1);
+      bool acc = false; T tNew = 0; uint32_t aux = 0;
 #pragma unroll
-    for (int f = 5; f >= 0; --f) {
-      uint32_t plane; T i0, i1, j0, j1, k, t1;
-      cuboidFace<T>(f, mn, mx, plane, i0, i1, j0, j1, k);
-      if (rectT<T>(plane, i0, i1, j0, j1, k, tr.o, tr.d, tr.tmin, tr.tbest, t1)) {
-        if (!acc) { acc = true; tNew = t1; aux = (uint32_t)f; }
-        else if (t1 < tNew) { tNew = t1; aux = (uint32_t)f; }
+      for (int f = 5; f >= 0; --f) {
+        uint32_t plane; T i0, i1, j0, j1, k, t1;
+        cuboidFace<T>(f, mn, mx, plane, i0, i1, j0, j1, k);
+        if (rectT<T>(plane, i0, i1, j0, j1, k, tr.o, tr.d, tr.tmin, tr.tbest, t1)) {
+          if (!acc) { acc = true; tNew = t1; aux = (uint32_t)f; }
+          else if (t1 < tNew) { tNew = t1; aux = (uint32_t)f; }
+        }
       }
+      if (acc) travAccept<T>(tr, tNew, ref, aux);
     }
-    if (acc) travAccept<T>(tr, tNew, ref, aux);
+    if (ref2 == kNone) break;
+    ref = ref2; ref2 = kNone;
   }
   tr.next();
 }
@@ -198,7 +221,7 @@ template <class T, bool FAST> RTB_D void travReframe(const DScene<T>& sc, Trav<T
 // the rare kinds: frames, markers, media, Unhittable
 template <class T, int INSTR, bool FAST>
 RTB_D void stepRare(const DScene<T>& sc, Trav<T>& tr, Rng& rng, Instr<INSTR>& ins) {
-  const uint32_t ref = tr.cur, kind = ref >> 28, idx = ref & 0x0fffffffu;
+  const uint32_t ref = tr.cur, kind = ref >> 28, idx = ref & kIdxMask;
   if (kind == K_TRANSLATE || kind == K_ROTATE) {
     ins.visit(ref);
     const uint32_t child = (kind == K_TRANSLATE) ? bitsOf(ldq(sc.translates + idx).w) : bitsOf(ldq(sc.rotates + idx).w);

@@ -213,8 +213,9 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
     }
 
     if constexpr (INSTR == 1) {  // scheduler statistics (RtStats::sched)
-      const int n0 = __popc(__ballot_sync(0xffffffffu, cls == 0)), n1 = __popc(__ballot_sync(0xffffffffu, cls == 1)), n2 = __popc(__ballot_sync(0xffffffffu, cls == 2)),
-                n3 = __popc(__ballot_sync(0xffffffffu, cls == 3)), n4 = __popc(__ballot_sync(0xffffffffu, cls == 4));
+      const int sc_ = cls;
+      const int n0 = __popc(__ballot_sync(0xffffffffu, sc_ == 0)), n1 = __popc(__ballot_sync(0xffffffffu, sc_ == 1)), n2 = __popc(__ballot_sync(0xffffffffu, sc_ == 2)),
+                n3 = __popc(__ballot_sync(0xffffffffu, sc_ == 3)), n4 = __popc(__ballot_sync(0xffffffffu, sc_ == 4));
       if (lane == 0) {
         const int served = pick == 0 ? n0 : pick == 1 ? n1 : pick == 2 ? n2 : pick == 3 ? n3 : n4;
         ++sch[pick]; sch[5 + pick] += (unsigned)served; sch[10] += n0; sch[11] += n1; sch[12] += n2; sch[13] += n3; sch[14] += n4; ++sch[15];

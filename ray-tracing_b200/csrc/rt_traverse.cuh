@@ -122,7 +122,9 @@ template <class T, int INSTR, bool FAST>
 RTB_D void stepNode(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
   const uint32_t idx = tr.cur & kIdxMask;
   ins.visit(tr.cur); ins.boxTest();
-  const Q4<T> lo = ldq(sc.nodes + 2 * (size_t)idx), hi = ldq(sc.nodes + 2 * (size_t)idx + 1);
+  // byte offset of the node record = index * 2 * sizeof(Q4<T>): the shift drops the kind nibble and the (clear) pair bit with it
+  const Q4<T>* np = reinterpret_cast<const Q4<T>*>(reinterpret_cast<const char*>(sc.nodes) + ((size_t)(tr.cur << 5) * (sizeof(T) / 4)));
+  const Q4<T> lo = ldq(np), hi = ldq(np + 1);
   bool pass;
   if constexpr (!FAST && sizeof(T) == 4) {
     bool ok = (tr.flags & F_MODE_GENERIC) == 0u;  // no axis in the generic division mode

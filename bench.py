@@ -33,6 +33,17 @@ SCENE_SPP = {"random_book1": 1024, "random": 1024, "next_week_final": 256, "corn
 FP32_PEAK_TFLOPS_NOMINAL = 148 * 128 * 2 * 1.965e9 / 1e12  # FFMA = 2 flop; no measured figure in MEASURED_PEAKS.json
 
 
+def measured_traffic(scene, W, H, spp):
+    """DRAM bytes of one renderKernel launch of exactly this workload, from the committed ncu capture (profiles/r1_traffic.json); None if not captured."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json"))).get(scene)
+    except (OSError, ValueError):
+        return None
+    if not t or (t["width"], t["height"], t["spp"]) != (W, H, spp):
+        return None
+    return t["dram_bytes_read"] + t["dram_bytes_write"]
+
+
 def peaks():
     try:
         return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -254,7 +265,7 @@ def main():
             "config": {"workload": SCENE_DOC[args.scene], "scene": args.scene, "width": W, "height": H, "spp_per_gpu_per_step": spp, "max_depth": 50,
                        "seed": "randGen 1024", "lights": "HEAD", "parallelism": "spp-sharded x%d + ncclReduce" % world, "l2": "flushed between steps (256 MiB write)",
                        "arithmetic": "fast-math" if args.fast else "literal (no FMA contraction, IEEE div/sqrt)", "finite_pixel_fraction": finite_frac},
-            "roofline": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak, "traffic": None,
+            "roofline": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak, "traffic": measured_traffic(args.scene, W, H, spp),
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst)" if pk else "fallback 6.65 TB/s", "kernel": "renderKernel", "kernel_ms": kernel_ms,
                          "algorithmic_bytes_per_sample": bytes_ps, "per_sample": per_sample,
                          "note": "scene is L1/L2-resident (KBs..MBs); the binding roofline is FP32 issue under divergence, see roofline_fp32"},

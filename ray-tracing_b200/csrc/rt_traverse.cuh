@@ -133,7 +133,8 @@ RTB_D void stepNode(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
     const bool bz = slabHoisted(lo.z, hi.z, tr.o.z, tr.d.z, tr.inv.z, tr.tmin, tr.tbest, ok);
     pass = bx && by && bz;
     // a quotient left the validated range of the hoisted reciprocal (e.g. an exact 0), or generic mode: the literal test decides
-    if (!ok) pass = boxLiteral(lo.x, lo.y, lo.z, hi.x, hi.y, hi.z, tr.o.x, tr.o.y, tr.o.z, tr.d.x, tr.d.y, tr.d.z, tr.tmin, tr.tbest);
+    if (!ok) pass = boxFallback(lo.x, lo.y, lo.z, hi.x, hi.y, hi.z, tr.o.x, tr.o.y, tr.o.z, tr.d.x, tr.d.y, tr.d.z, tr.inv.x, tr.inv.y, tr.inv.z,
+                                 (tr.flags & F_MODE_GENERIC) != 0u, tr.tmin, tr.tbest);
   } else {
     const bool bx = slab<T, FAST>(lo.x, hi.x, tr.o.x, tr.d.x, tr.inv.x, tr.tmin, tr.tbest);
     const bool by = slab<T, FAST>(lo.y, hi.y, tr.o.y, tr.d.y, tr.inv.y, tr.tmin, tr.tbest);

@@ -118,6 +118,7 @@ def host():
         L.rth_scene_desc.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.rth_scene_g1.argtypes = [C.c_void_p, C.c_void_p]
         L.rth_run_render.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        L.rth_write_image.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_int]
         _host = L
     return _host
 

@@ -148,3 +148,12 @@ def tonemap(rgb_sum, total_samples):
     out = np.zeros(rgb_sum.shape, np.uint8)
     _check(core().rt_tonemap(_p(rgb_sum), rgb_sum.size, total_samples, _p(out)))
     return out
+
+
+def write_image(path, rgb8, binary=False):
+    """The image file app/Main.hs:58-62 prints for a rendered frame (uint8 [H, W, 3], top row first): "P3" text rows in
+    printRow's format (Lib.hs:299-305), or "P6" binary with the same header."""
+    rgb8 = np.ascontiguousarray(rgb8, dtype=np.uint8)
+    H, W, _ = rgb8.shape
+    if host().rth_write_image(str(path).encode(), _p(rgb8), W, H, int(bool(binary))) != 0:
+        raise RuntimeError(host().rth_last_error().decode())

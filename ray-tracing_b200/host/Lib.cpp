@@ -1,5 +1,6 @@
 // host/Lib.cpp — see Lib.hpp.  Reference lines cited are src/Lib.hs unless noted.
 #include "Lib.hpp"
+#include <string>
 
 #include <algorithm>
 #include <cmath>
@@ -312,6 +313,38 @@ static uint8_t scaleColor(double x) {
   return (f == f) ? (uint8_t)(int)f : (uint8_t)0;  // floor NaN :: Word8 is platform-defined in GHC; 0 here
 }
 RGB albedoToColor(const Albedo& a) { return RGB{scaleColor(a.v.x), scaleColor(a.v.y), scaleColor(a.v.z)}; }
+
+std::string showRow(const std::vector<RGB>& row) {
+  std::string s;
+  s.reserve(row.size() * 12);
+  for (size_t x = 0; x < row.size(); ++x) {
+    if (x) s += ' ';
+    s += std::to_string((int)row[x].r); s += ' '; s += std::to_string((int)row[x].g); s += ' '; s += std::to_string((int)row[x].b);
+  }
+  return s;
+}
+void printRow(FILE* handle, int imageHeight, int i, const std::vector<RGB>& row) {
+  std::fprintf(stderr, "\rRendering row %d of %d", i, imageHeight);
+  const std::string s = showRow(row);
+  std::fwrite(s.data(), 1, s.size(), handle);
+  std::fputc('\n', handle);
+}
+void writeImage(FILE* handle, const std::vector<std::vector<RGB>>& rows, bool binary, bool progress) {
+  const int H = (int)rows.size(), W = H ? (int)rows[0].size() : 0;
+  std::fprintf(handle, "%s\n%d %d\n255\n", binary ? "P6" : "P3", W, H);
+  for (int i = 0; i < H; ++i) {
+    if (binary) {
+      static_assert(sizeof(RGB) == 3, "RGB is three packed bytes");
+      std::fwrite(rows[i].data(), 3, rows[i].size(), handle);
+    } else if (progress) {
+      printRow(handle, H, i + 1, rows[i]);
+    } else {
+      const std::string s = showRow(rows[i]);
+      std::fwrite(s.data(), 1, s.size(), handle);
+      std::fputc('\n', handle);
+    }
+  }
+}
 
 std::vector<std::vector<RGB>> runRender(const RenderStaticEnv& env, std::vector<RandGen> gens) {
   if (gens.empty()) throw std::runtime_error("runRender: no generators");

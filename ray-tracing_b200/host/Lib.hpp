@@ -8,6 +8,7 @@
 #include <cstdint>
 #include <string>
 #include <utility>
+#include <cstdio>
 #include <vector>
 
 #include "../../include/rt_abi.h"
@@ -130,5 +131,11 @@ RenderStaticEnv mkRenderStaticEnv(const Arena& arena, Scene s, Camera c, std::pa
 // with rt_last_error() if the device path fails — there is no CPU fallback.
 std::vector<std::vector<RGB>> runRender(const RenderStaticEnv& env, std::vector<RandGen> gens);
 RGB albedoToColor(const Albedo& a);  // Lib.hs:287-292 (host-side, as in the reference)
+// Lib.hs:299-305: one text row "r g b r g b ..." + newline on `handle`, progress "\rRendering row i of H" on stderr
+std::string showRow(const std::vector<RGB>& row);
+void printRow(FILE* handle, int imageHeight, int i, const std::vector<RGB>& row);
+// The image file app/Main.hs:58-62 prints: "P3\nW H\n255\n" + printRow per row (binary = false), or the same header
+// with P6 and raw bytes (binary = true; SURVEY 8(f) rank 2: at 4K the text path dominates once rendering takes seconds)
+void writeImage(FILE* handle, const std::vector<std::vector<RGB>>& rows, bool binary, bool progress);
 
 }  // namespace Lib

@@ -85,4 +85,17 @@ int rth_run_render(void* p, int W, int H, int numSamples, int maxDepth, uint8_t*
   } catch (const std::exception& e) { g_err = e.what(); return -1; }
 }
 
+// app/Main.hs:58-62 for an already rendered frame: P3 text (the reference's format) or P6 binary
+int rth_write_image(const char* path, const uint8_t* rgb8, int W, int H, int binary) {
+  try {
+    FILE* f = std::fopen(path, "wb");
+    if (!f) throw std::runtime_error(std::string("cannot open ") + path);
+    std::vector<std::vector<RGB>> rows((size_t)H, std::vector<RGB>((size_t)W));
+    for (int r = 0; r < H; ++r) for (int x = 0; x < W; ++x) { const uint8_t* o = rgb8 + ((size_t)r * W + x) * 3; rows[r][x] = RGB{o[0], o[1], o[2]}; }
+    writeImage(f, rows, binary != 0, false);
+    std::fclose(f);
+    return 0;
+  } catch (const std::exception& e) { g_err = e.what(); return -1; }
+}
+
 }  // extern "C"

@@ -122,3 +122,19 @@ def test_product_does_not_touch_oracle():
     for so in ("librt_b200.so", "librt_host.so"):
         out = subprocess.check_output(["ldd", os.path.join(pkg, so)]).decode()
         assert "oracle" not in out
+
+
+def test_write_image_formats(R, tmp_path):
+    """writeImage: P3 text in printRow's format (Lib.hs:299-305, app/Main.hs:58-62) and P6 binary; host-only, no GPU."""
+    from ray_tracing_b200._scene import write_image
+    rng = np.random.default_rng(5)
+    img = rng.integers(0, 256, size=(3, 4, 3), dtype=np.uint8)
+    p3, p6 = tmp_path / "a.ppm", tmp_path / "b.ppm"
+    write_image(p3, img, binary=False)
+    write_image(p6, img, binary=True)
+    lines = p3.read_text().split("\n")
+    assert lines[:3] == ["P3", "4 3", "255"] and lines[-1] == ""
+    for r in range(3):
+        assert lines[3 + r] == " ".join(str(int(v)) for v in img[r].reshape(-1))  # unwords (show <$> row), show RGB = "r g b"
+    raw = p6.read_bytes()
+    assert raw.startswith(b"P6\n4 3\n255\n") and raw[len(b"P6\n4 3\n255\n"):] == img.tobytes()

@@ -138,3 +138,25 @@ def test_write_image_formats(R, tmp_path):
         assert lines[3 + r] == " ".join(str(int(v)) for v in img[r].reshape(-1))  # unwords (show <$> row), show RGB = "r g b"
     raw = p6.read_bytes()
     assert raw.startswith(b"P6\n4 3\n255\n") and raw[len(b"P6\n4 3\n255\n"):] == img.tobytes()
+
+
+def test_haskell_binding_matches_header():
+    """integration/haskell/LibB200.hsc cannot be compiled here (no GHC): at least every struct field it pokes and every
+    constant it names must exist in include/rt_abi.h, every RtSceneDesc member must be filled, and every entry point it
+    imports must be exported by the built library."""
+    h = open(os.path.join(ROOT, "include", "rt_abi.h")).read()
+    s = open(os.path.join(ROOT, "integration", "haskell", "LibB200.hsc")).read()
+    for st, f in re.findall(r"#\{(?:poke|ptr)\s+(\w+),\s*(\w+)\}", s):
+        body = h[h.index("typedef struct " + st):h.index("} " + st + ";")]
+        assert re.search(r"\b" + f + r"\b", body), (st, f)
+    for c in re.findall(r"#\{const\s+(\w+)\}", s):
+        assert re.search(r"\b" + c + r"\b", h), c
+    body = h[h.index("typedef struct RtSceneDesc"):h.index("} RtSceneDesc;")]
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    declared = set(re.findall(r"(\w+)(?:\[\d+\])?;", body))
+    filled = set(re.findall(r"#\{(?:poke|ptr)\s+RtSceneDesc,\s*(\w+)\}", s))
+    assert declared == filled, declared ^ filled
+    import ctypes
+    lib = ctypes.CDLL(os.path.join(ROOT, "ray-tracing_b200", "librt_b200.so"))
+    for sym in re.findall(r'foreign import ccall \w+\s+"(\w+)"', s):
+        assert hasattr(lib, sym), sym

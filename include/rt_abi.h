@@ -235,6 +235,21 @@ int rt_tonemap(const double* rgb_sum, uint32_t n, uint32_t total_samples, uint8_
  * *mismatches == 0.  Not part of the reference path. */
 int rt_selftest_division(uint64_t n, uint64_t seed, uint64_t* checked, uint64_t* mismatches);
 
+/* makeBVH (Lib.hs:941-961) built on the device, tree-identical to the host recursion: the node's objects are sorted stably by
+ * box_min[axis] (Data.Sequence.sortBy of boxCompare, Lib.hs:963-968), split at n `div` 2; one object -> BVHNode h h (948),
+ * two objects -> ordered by `comparator h1 h2 == LT`, ties swapped (949-952); box = surroundingBox of the children (929-939).
+ *   n, leaf_box[n][6]   boundingBox (Lib.hs:905-927) of each object of the sequence, in sequence order: min.xyz max.xyz
+ *   node_axis[n_nodes]  `floor <$> randomDoubleRM 0 3` of every node in PRE-ORDER (the order the RandomState monad draws
+ *                       them: a node, then its whole left subtree, then the right one); n_nodes = rt_bvh_node_count(n)
+ *   outputs, indexed by pre-order node id (root = 0): node_box[n_nodes][6], node_size[n_nodes] (bvh_size), and the children:
+ *                       bit 31 set = a node (low bits: its pre-order id), clear = an object (index into leaf_box)
+ *   build_ms            optional: device time of the build including its copies
+ * NaN box coordinates are rejected (`compare` is not an order on them).  Replaces the host-side makeBVH for large scenes
+ * (SURVEY 8(f) rank 3); the hot path never calls it. */
+uint32_t rt_bvh_node_count(uint32_t n);
+int rt_bvh_build(uint32_t n, const double* leaf_box, const uint8_t* node_axis, uint32_t n_nodes, double* node_box, uint32_t* node_left,
+                 uint32_t* node_right, uint32_t* node_size, int device, double* build_ms);
+
 void rt_shutdown(void);
 
 #ifdef __cplusplus

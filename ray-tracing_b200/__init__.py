@@ -65,7 +65,7 @@ class RtLimits(C.Structure):
 
 
 ABI_SYMBOLS = ["rt_abi_version", "rt_last_error", "rt_device_count", "rt_get_limits", "rt_scene_create", "rt_scene_destroy",
-               "rt_render", "rt_render_device", "rt_render_counted", "rt_trace", "rt_texture_value", "rt_tonemap", "rt_selftest_division", "rt_shutdown"]
+               "rt_render", "rt_render_device", "rt_render_counted", "rt_trace", "rt_texture_value", "rt_tonemap", "rt_selftest_division", "rt_bvh_node_count", "rt_bvh_build", "rt_shutdown"]
 
 _core = None
 _host = None
@@ -97,6 +97,9 @@ def core():
                                C.c_uint32] + [C.c_void_p] * 8
         L.rt_texture_value.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
         L.rt_tonemap.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
+        L.rt_bvh_node_count.restype = C.c_uint32
+        L.rt_bvh_node_count.argtypes = [C.c_uint32]
+        L.rt_bvh_build.argtypes = [C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.rt_selftest_division.argtypes = [C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         _core = L
     return _core
@@ -118,6 +121,8 @@ def host():
         L.rth_scene_desc.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.rth_scene_g1.argtypes = [C.c_void_p, C.c_void_p]
         L.rth_run_render.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        L.rth_set_device_bvh.argtypes = [C.c_int]
+        L.rth_last_device_bvh_ms.restype = C.c_double
         L.rth_write_image.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_int]
         _host = L
     return _host

@@ -157,3 +157,18 @@ def write_image(path, rgb8, binary=False):
     H, W, _ = rgb8.shape
     if host().rth_write_image(str(path).encode(), _p(rgb8), W, H, int(bool(binary))) != 0:
         raise RuntimeError(host().rth_last_error().decode())
+
+
+def bvh_build(leaf_box, node_axis, device=-1):
+    """rt_bvh_build: the reference's makeBVH on the device.  leaf_box [n, 6] float64, node_axis [N(n)] uint8 in pre-order.
+    Returns dict(box [N, 6], left [N], right [N], size [N], ms); children with bit 31 set are pre-order node ids."""
+    leaf_box = np.ascontiguousarray(leaf_box, dtype=np.float64)
+    node_axis = np.ascontiguousarray(node_axis, dtype=np.uint8)
+    n = leaf_box.shape[0]
+    N = core().rt_bvh_node_count(n)
+    if node_axis.shape[0] != N:
+        raise ValueError("node_axis must have rt_bvh_node_count(n) = %d entries" % N)
+    box = np.zeros((N, 6)); left = np.zeros(N, np.uint32); right = np.zeros(N, np.uint32); size = np.zeros(N, np.uint32)
+    ms = C.c_double(0.0)
+    _check(core().rt_bvh_build(n, _p(leaf_box), _p(node_axis), N, _p(box), _p(left), _p(right), _p(size), device, C.byref(ms)))
+    return dict(box=box, left=left, right=right, size=size, ms=ms.value)

@@ -361,6 +361,8 @@ int renderHost(rt_scene_t scene, const RtRenderParams* params, double* out, RtSt
 
 }  // namespace
 
+namespace rtb { void setLastError(const std::string& s) { g_err = s; } }  // for the other translation units of the library
+
 extern "C" {
 
 int rt_abi_version(void) { return RT_ABI_VERSION; }

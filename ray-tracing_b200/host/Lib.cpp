@@ -154,7 +154,35 @@ Box Arena::boundingBox(Hittable h) const {
   }
 }
 
+size_t Arena::deviceBVHMin = 0;
+double Arena::lastDeviceBVHms = 0.0;
+
 Hittable Arena::makeBVH(RandGen& g, const std::vector<Hittable>& htbls) {
+  if (deviceBVHMin && htbls.size() >= deviceBVHMin) {
+    // The device build needs the leaf boxes and every node's axis draw.  The recursion draws one axis per node, a node before
+    // its left subtree before its right subtree, so the pre-order axis array is the next N(n) draws of the generator.
+    const size_t n = htbls.size();
+    const uint32_t N = rt_bvh_node_count((uint32_t)n);
+    std::vector<double> boxes(n * 6);
+    for (size_t i = 0; i < n; ++i) {
+      const Box b = boundingBox(htbls[i]);
+      double* o = &boxes[i * 6];
+      o[0] = b.box_min.x; o[1] = b.box_min.y; o[2] = b.box_min.z; o[3] = b.box_max.x; o[4] = b.box_max.y; o[5] = b.box_max.z;
+    }
+    std::vector<uint8_t> axes(N);
+    for (uint32_t k = 0; k < N; ++k) axes[k] = (uint8_t)(int)std::floor(randomDoubleRM(g, 0, 3));
+    std::vector<double> nbox((size_t)N * 6); std::vector<uint32_t> nl(N), nr(N), ns(N);
+    if (rt_bvh_build((uint32_t)n, boxes.data(), axes.data(), N, nbox.data(), nl.data(), nr.data(), ns.data(), -1, &lastDeviceBVHms) != RT_OK)
+      throw std::runtime_error(std::string("rt_bvh_build: ") + rt_last_error());
+    const uint32_t base = (uint32_t)nodes_.size();
+    nodes_.resize((size_t)base + N);
+    auto child = [&](uint32_t c) { return (c & 0x80000000u) ? (uint32_t)RT_REF(RT_BVH_NODE, base + (c & 0x7fffffffu)) : htbls[c].ref; };
+    for (uint32_t k = 0; k < N; ++k) {
+      const double* b = &nbox[(size_t)k * 6];
+      nodes_[base + k] = NodeO{child(nl[k]), child(nr[k]), Box{Vec3{b[0], b[1], b[2]}, Vec3{b[3], b[4], b[5]}}, ns[k]};
+    }
+    return Hittable{RT_REF(RT_BVH_NODE, base)};
+  }
   const int axis = (int)std::floor(randomDoubleRM(g, 0, 3));
   const size_t n = htbls.size();
   if (n == 0) throw std::runtime_error("makeBVH: empty sequence");

@@ -77,6 +77,10 @@ class Arena {
   Hittable rotate(Axis axis, double angleDeg, Hittable h);
   Hittable constantMedium(double density, Texture tex, Hittable boundary);
   Hittable makeBVH(RandGen& g, const std::vector<Hittable>& htbls);  // Lib.hs:941-961 (Maybe (Time,Time) is never read)
+  // Sequences of at least this many objects are built by rt_bvh_build on the device (same tree, same generator state
+  // afterwards); 0 = always the host recursion.  Process-wide default, set by rth_set_device_bvh / RTB_DEVICE_BVH_MIN.
+  static size_t deviceBVHMin;
+  static double lastDeviceBVHms;  // device time of the most recent rt_bvh_build issued from makeBVH
   Box boundingBox(Hittable h) const;                                 // Lib.hs:905-927
 
   // flattened, canonically numbered copy of everything reachable from (world, lights): the RtSceneDesc arrays

@@ -1,6 +1,8 @@
 // host/capi.cpp — C entry points over the host-side mirror (Lib.hpp / Scenes.hpp) for ctypes callers (tests, bench.py).
 // Builds a reference scene by name with the mirrored constructors, flattens it, and hands out the RtSceneDesc that
 // goes through the C ABI of librt_b200.so.
+#include <cstdlib>
+#include <algorithm>
 #include <cstring>
 #include <memory>
 #include <stdexcept>
@@ -32,12 +34,17 @@ extern "C" {
 
 const char* rth_last_error() { return g_err.c_str(); }
 
+// makeBVH of sequences with at least min_objects objects goes to rt_bvh_build (0 = host recursion only); returns the old value
+int rth_set_device_bvh(int min_objects) { const int old = (int)Arena::deviceBVHMin; Arena::deviceBVHMin = min_objects > 0 ? (size_t)min_objects : 0; return old; }
+double rth_last_device_bvh_ms() { return Arena::lastDeviceBVHms; }
+
 // names: cornell cornell_smoke simple_light earth two_perlin two_spheres random_book1 random next_week_final synthetic
 void* rth_scene_create(const char* name, int64_t seed, double t0, double t1, const uint8_t* earth, int ew, int eh, int lit, int synthN) {
   try {
     auto h = std::make_unique<HostHandle>();
     h->name = name; h->synthN = synthN;
     if (earth && ew > 0 && eh > 0) { h->earth.w = (uint32_t)ew; h->earth.h = (uint32_t)eh; h->earth.rgb.assign(earth, earth + (size_t)ew * eh * 3); }
+    if (const char* v = std::getenv("RTB_DEVICE_BVH_MIN")) Arena::deviceBVHMin = (size_t)std::max(0, std::atoi(v));
     Arena& A = h->arena;
     RandGen gen = randGen(seed);
     const std::string n = name;

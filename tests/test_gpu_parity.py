@@ -302,3 +302,78 @@ def test_full_size_properties(gpu, O, earth, name, w, h):
     ref, _ = osc.render(w, h, 2, depth=50, prec=O.PREC_F32, mode=1, seed=17)
     media = name == "next_week_final"
     _cmp_images(img, ref, frac_min=0.80 if media else 0.90, mean_tol=0.04 if media else 0.02)
+
+
+# ---- makeBVH on the device (rt_bvh_build)
+def _ref_make_bvh(boxes, axes):
+    """The reference recursion (Lib.hs:941-961) on plain arrays: pre-order ids, stable sort, n div 2 split, tie rules."""
+    NODE = 0x80000000
+    N = len(axes)
+    box = np.zeros((N, 6)); left = np.zeros(N, np.uint32); right = np.zeros(N, np.uint32); size = np.zeros(N, np.uint32)
+    counter = [0]
+
+    def hmin(x, y): return np.where(x <= y, x, y)
+    def hmax(x, y): return np.where(x <= y, y, x)
+
+    def go(idx):
+        me = counter[0]; counter[0] += 1
+        ax = int(axes[me]); n = len(idx)
+        if n == 1:
+            l = r = int(idx[0]); bl = br = boxes[l]
+        elif n == 2:
+            h1, h2 = int(idx[0]), int(idx[1])
+            l, r = (h1, h2) if boxes[h1, ax] < boxes[h2, ax] else (h2, h1)
+            bl, br = boxes[l], boxes[r]
+        else:
+            s = idx[np.argsort(boxes[idx, ax], kind="stable")]
+            li = go(s[:n // 2]); ri = go(s[n // 2:])
+            l, r = li | NODE, ri | NODE
+            bl, br = box[li], box[ri]
+        box[me, :3] = hmin(bl[:3], br[:3]); box[me, 3:] = hmax(bl[3:], br[3:])
+        left[me], right[me], size[me] = l, r, n
+        return me
+
+    go(np.arange(len(boxes)))
+    assert counter[0] == N
+    return box, left, right, size
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 7, 17, 100, 1000, 4097, 60000])
+def test_device_bvh_equals_reference_recursion(gpu, n):
+    """Bit-identical tree for every size class, with heavy key ties (quantised coordinates, both zeros) so that the stable
+    sort and the two-object tie rule are exercised."""
+    from ray_tracing_b200._scene import bvh_build
+    rng = np.random.default_rng(n)
+    lo = np.round(rng.normal(size=(n, 3)) * 4) / 4          # many equal keys
+    lo[rng.random((n, 3)) < 0.1] = 0.0
+    lo[rng.random((n, 3)) < 0.05] = -0.0                    # compare (-0.0) 0.0 == EQ
+    boxes = np.concatenate([lo, lo + rng.random((n, 3))], axis=1)
+    N = gpu.core().rt_bvh_node_count(n)
+    axes = rng.integers(0, 3, size=N).astype(np.uint8)
+    got = bvh_build(boxes, axes)
+    box, left, right, size = _ref_make_bvh(boxes, axes)
+    assert np.array_equal(got["left"], left) and np.array_equal(got["right"], right) and np.array_equal(got["size"], size)
+    assert np.array_equal(got["box"].view(np.uint64), box.view(np.uint64))  # bit-exact, signed zeros included
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,kw", [("synthetic", dict(synth_n=70)), ("random", {}), ("next_week_final", {})])
+def test_device_bvh_builds_the_same_scene(gpu, name, kw):
+    """The mirrored makeBVH with its sequences sent to the device flattens to exactly the arrays of the host recursion
+    (same tree, same generator state afterwards), so every downstream parity result carries over."""
+    from ray_tracing_b200._scene import desc_arrays
+    host = gpu.host()
+    a = gpu.HostScene(name, **kw)
+    da = desc_arrays(a.desc(64, 48).contents)
+    old = host.rth_set_device_bvh(3)
+    try:
+        b = gpu.HostScene(name, **kw)
+    finally:
+        host.rth_set_device_bvh(old)
+    db = desc_arrays(b.desc(64, 48).contents)
+    assert host.rth_last_device_bvh_ms() > 0
+    assert da.keys() == db.keys()
+    for k in da:
+        assert np.array_equal(np.asarray(da[k]), np.asarray(db[k])), k
+    assert np.array_equal(a.g1(), b.g1())

@@ -15,7 +15,7 @@ SCENES = ["cornell", "cornell_smoke", "simple_light", "earth", "two_perlin", "tw
 
 def test_abi_exports_every_declared_symbol(R):
     hdr = open(os.path.join(ROOT, "include", "rt_abi.h")).read()
-    declared = set(re.findall(r"^(?:int|void|const char\*)\s+(rt_[a-z_]+)\s*\(", hdr, re.M))
+    declared = set(re.findall(r"^(?:int|void|uint32_t|const char\*)\s+(rt_[a-z_]+)\s*\(", hdr, re.M))
     assert declared == set(R.ABI_SYMBOLS), declared ^ set(R.ABI_SYMBOLS)
     L = R.core()
     for s in declared:

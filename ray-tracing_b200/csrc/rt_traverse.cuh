@@ -125,6 +125,12 @@ RTB_D void stepNode(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
   // byte offset of the node record = index * 2 * sizeof(Q4<T>): the shift drops the kind nibble and the (clear) pair bit with it
   const Q4<T>* np = reinterpret_cast<const Q4<T>*>(reinterpret_cast<const char*>(sc.nodes) + ((size_t)(tr.cur << 5) * (sizeof(T) / 4)));
   const Q4<T> lo = ldq(np), hi = ldq(np + 1);
+  // pass: go left, right child stacked -- or, when both children are leaves of one class, one pair step and nothing stacked
+  auto descend = [&]() {
+    const uint32_t lc = bitsOf(lo.w);
+    if (lc & kPairBit) tr.cur = (lc & 0xf0000000u) | kPairBit | idx;
+    else { tr.push(bitsOf(hi.w)); tr.cur = lc; }
+  };
   bool pass;
   if constexpr (!FAST && sizeof(T) == 4) {
     bool ok = (tr.flags & F_MODE_GENERIC) == 0u;  // no axis in the generic division mode
@@ -132,20 +138,21 @@ RTB_D void stepNode(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
     const bool by = slabHoisted(lo.y, hi.y, tr.o.y, tr.d.y, tr.inv.y, tr.tmin, tr.tbest, ok);
     const bool bz = slabHoisted(lo.z, hi.z, tr.o.z, tr.d.z, tr.inv.z, tr.tmin, tr.tbest, ok);
     pass = bx && by && bz;
-    // a quotient left the validated range of the hoisted reciprocal (e.g. an exact 0), or generic mode: the literal test decides
-    if (!ok) pass = boxFallback(lo.x, lo.y, lo.z, hi.x, hi.y, hi.z, tr.o.x, tr.o.y, tr.o.z, tr.d.x, tr.d.y, tr.d.z, tr.inv.x, tr.inv.y, tr.inv.z,
-                                 (tr.flags & F_MODE_GENERIC) != 0u, tr.tmin, tr.tbest);
+    if (!ok) {
+      // a quotient left the validated range of the hoisted reciprocal (e.g. an exact 0), or generic mode: the out-of-line test
+      // decides.  Its own copy of the two outcomes keeps `pass` a predicate (not a register merged after the call) in the hot path.
+      if (boxFallback(lo.x, lo.y, lo.z, hi.x, hi.y, hi.z, tr.o.x, tr.o.y, tr.o.z, tr.d.x, tr.d.y, tr.d.z, tr.inv.x, tr.inv.y, tr.inv.z,
+                      (tr.flags & F_MODE_GENERIC) != 0u, tr.tmin, tr.tbest)) descend();
+      else tr.next();
+      return;
+    }
   } else {
     const bool bx = slab<T, FAST>(lo.x, hi.x, tr.o.x, tr.d.x, tr.inv.x, tr.tmin, tr.tbest);
     const bool by = slab<T, FAST>(lo.y, hi.y, tr.o.y, tr.d.y, tr.inv.y, tr.tmin, tr.tbest);
     const bool bz = slab<T, FAST>(lo.z, hi.z, tr.o.z, tr.d.z, tr.inv.z, tr.tmin, tr.tbest);
     pass = bx && by && bz;
   }
-  if (pass) {
-    const uint32_t lc = bitsOf(lo.w);
-    if (lc & kPairBit) tr.cur = (lc & 0xf0000000u) | kPairBit | idx;  // both children are leaves of one class: one pair step, nothing stacked
-    else { tr.push(bitsOf(hi.w)); tr.cur = lc; }
-  } else tr.next();
+  if (pass) descend(); else tr.next();
 }
 
 template <class T, class S, int INSTR>

@@ -52,7 +52,7 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons sampled every 200 ms during the timed region."""
+    """nvidia-smi clocks + throttle reasons sampled every 500 ms during the timed regions (each query can delay a kernel launch by tens of ms: the wall-clocked e2e loop sees that)."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, index):
@@ -60,7 +60,7 @@ class ClockSampler:
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "200"],
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "500"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
@@ -218,7 +218,6 @@ def main():
         t = torch.tensor([ms], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    clocks = sampler.stop() if rank == 0 else None
     kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in k_ev]))
     value = args.steps * W * H * total_spp / (ms / 1e3)
     finite_frac = float(torch.isfinite(fb).all(dim=2).float().mean().item()) if rank == 0 else None
@@ -229,9 +228,12 @@ def main():
 
     def e2e_step(i):
         if world == 1:
+            tq = time.perf_counter()
             d2 = pkg.DeviceScene(desc, local)
-            d2.render(W, H, spp, depth=50, seed=500 + i, out=host_out, precision=args.precision, flags=flags)
+            _, st = d2.render(W, H, spp, depth=50, seed=500 + i, out=host_out, precision=args.precision, flags=flags)
             d2.destroy()
+            if os.environ.get("RTB_BENCH_DEBUG"):
+                print("e2e step %d: %.1f ms (kernel %.1f ms)" % (i, (time.perf_counter() - tq) * 1e3, st["kernel_ms"]), file=sys.stderr)
         else:
             d2 = pkg.DeviceScene(desc, local)
             _dist.render_sharded(d2, W, H, total_spp, 50, 500 + i, fb, stream=stream, precision=args.precision, flags=flags)
@@ -250,6 +252,9 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
     e2e_value = args.steps * W * H * total_spp / e2e_s
+    # the sampler runs through both timed regions and is stopped only here: terminating nvidia-smi stalls the context for up to a
+    # few hundred ms, which the device-timed loop does not see but the wall-clocked end-to-end loop would
+    clocks = sampler.stop() if rank == 0 else None
 
     if rank == 0:
         pk = peaks()

@@ -249,6 +249,50 @@ inline Camera syntheticCamera(int W, int H, int n) {
   return newCamera(V3d(0.9 * e, 0.45 * e, 0.9 * e), V3d(0, 0, 0), V3d(0, 1, 0), 40.0, (double)W / (double)H, 0.0, 10.0, 0.0, 1.0);
 }
 
+// API-coverage scene "quirks" (NOT in the reference; built only with the reference's constructors, Lib.hs:587-660, 726-761,
+// 789-791, 941-961): the combinations Scenes.hs never uses but Lib.hs supports, inside a Cornell-sized room —
+// Rotate about the X and Z axes (Lib.hs:763-787), three nested Translate/Rotate frames, a Rotate above a BVH, a one-object
+// makeBVH (Q3: BVHNode x x) in the world and in the light list, an XY rect in the light list (Q10: htblRandom falls back to
+// (1,0,0), htblPdfValue to 0), Metal with fuzz > 1 (Q12), a ConstantMedium with a Perlin phase texture around a rotated
+// cuboid, a checker of a checker and a Perlin texture (Lib.hs:496-503), a moving sphere next to all of them.
+inline Scene makeQuirksScene(const SceneArgs& a, SMGen gen) {
+  TexP pertext = makePerlin(gen, 0.05);
+  TexP chk = checkerTexture(checkerTexture(constantColor(0.2, 0.3, 0.1), constantColor(0.9, 0.9, 0.9)), pertext);
+  MatP white = lambertian(constantColor(0.73, 0.73, 0.73));
+  MatP red = lambertian(constantColor(0.65, 0.05, 0.05));
+  MatP mirror = metal(constantColor(0.8, 0.85, 0.9), 0.3);
+  MatP fuzzy = metal(constantColor(0.9, 0.6, 0.2), 2.0);
+  MatP glass = dielectric(1.5);
+  MatP light = diffuseLight(constantColor(15, 15, 15));
+  MatP dim = diffuseLight(constantColor(4, 4, 4));
+  HitP xzLight = rect(XZPlane, 163, 393, 177, 382, 554, light);
+  HitP sphereLight = sphere(V3d(460, 420, 120), 40, dim);
+  HitP xyLight = rect(XYPlane, 100, 250, 350, 500, 554, dim);
+  std::vector<HitP> cluster;
+  for (int i = 0; i < 12; ++i) {
+    V3d p = randomVec3DoubleRM(gen, 0, 120);
+    double r = randomDoubleRM(gen, 8, 20);
+    cluster.push_back(sphere(p, r, i % 3 == 0 ? glass : (i % 3 == 1 ? white : mirror)));
+  }
+  HitP clusterBVH = makeBVH(gen, cluster);
+  HitP lone = makeBVH(gen, {sphere(V3d(90, 60, 380), 60, fuzzy)});
+  Scene s;
+  s.world = makeBVH(gen, {rect(YZPlane, 0, 555, 0, 555, 555, mirror), rect(YZPlane, 0, 555, 0, 555, 0, red), xzLight, sphereLight, xyLight,
+                          rect(XZPlane, 0, 555, 0, 555, 0, lambertian(chk)), rect(XZPlane, 0, 555, 0, 555, 555, white),
+                          rect(XYPlane, 0, 555, 0, 555, 555, white),
+                          translate(V3d(360, 100, 260), rotate(XAxis, 25, cuboid(V3d(-60, -60, -60), V3d(60, 60, 60), white))),
+                          translate(V3d(200, 250, 250), rotate(ZAxis, -40, clusterBVH)),
+                          rotate(XAxis, 10, translate(V3d(420, 300, 300), rotate(ZAxis, 20, cuboid(V3d(-40, -40, -40), V3d(40, 40, 40), glass)))),
+                          lone,
+                          constantMedium(0.02, constantColor(0.9, 0.9, 0.9), sphere(V3d(140, 90, 150), 70, white)),
+                          constantMedium(0.03, pertext, translate(V3d(420, 80, 120), rotate(ZAxis, 30, cuboid(V3d(-50, -50, -50), V3d(50, 50, 50), white)))),
+                          movingSphere(V3d(280, 400, 300), V3d(310, 430, 300), a.t0, a.t1, 35, lambertian(constantColor(0.7, 0.3, 0.1)))});
+  // lightsMode 1: without the XY rect, whose (1,0,0) fallback direction makes the mixture pdf 0 on surfaces facing y or z (0/0, Q11)
+  s.lights = a.lightsMode == 1 ? makeBVH(gen, {xzLight, sphereLight}) : makeBVH(gen, {xzLight, sphereLight, xyLight});
+  s.g1 = gen;
+  return s;
+}
+
 inline Scene makeSceneByName(const std::string& name, const SceneArgs& a, int64_t seed) {
   SMGen gen = randGen(seed);
   Scene s;
@@ -262,12 +306,13 @@ inline Scene makeSceneByName(const std::string& name, const SceneArgs& a, int64_
   else if (name == "random") s = makeRandomScene(a, gen);
   else if (name == "next_week_final") s = makeNextWeekFinalScene(a, gen);
   else if (name == "synthetic") s = makeSyntheticScene(a, gen);
+  else if (name == "quirks") s = makeQuirksScene(a, gen);
   else throw std::runtime_error("unknown scene: " + name);
   s.number();
   return s;
 }
 inline Camera cameraByName(const std::string& name, int W, int H, int synthN) {
-  if (name == "cornell" || name == "cornell_smoke") return cornellCamera(W, H);
+  if (name == "cornell" || name == "cornell_smoke" || name == "quirks") return cornellCamera(W, H);
   if (name == "simple_light" || name == "earth" || name == "two_perlin" || name == "two_spheres") return twoSpheresSceneCamera(W, H);
   if (name == "random_book1" || name == "random") return randomSceneCamera(W, H);
   if (name == "next_week_final") return nextWeekFinalSceneCamera(W, H);

@@ -24,7 +24,7 @@ COUNTER_NAMES = ["paths", "bounces", "box_tests", "sphere_tests", "moving_tests"
                  "translate_visits", "rotate_visits", "medium_visits", "sphere_hits", "noise_calls", "texels", "queries",
                  "visits", "unhittable_visits"]
 SCENES = ["cornell", "cornell_smoke", "simple_light", "earth", "two_perlin", "two_spheres", "random_book1", "random",
-          "next_week_final", "synthetic"]
+          "next_week_final", "synthetic", "quirks"]
 
 
 class RtSceneDesc(C.Structure):
@@ -143,3 +143,4 @@ def load_earth():
 
 
 from ._scene import HostScene, DeviceScene, desc_arrays  # noqa: E402,F401
+from ._progressive import ProgressiveRender  # noqa: E402,F401

@@ -220,4 +220,46 @@ Camera syntheticCamera(std::pair<int, int> wh, int n) {
   return newCamera(point3(0.9 * e, 0.45 * e, 0.9 * e), point3(0, 0, 0), point3(0, 1, 0), 40.0, (double)wh.first / (double)wh.second, 0.0, 10.0, 0.0, 1.0);
 }
 
+// "quirks": an API-coverage scene that is NOT in Scenes.hs, built only with the reference's constructors (Lib.hs:587-660, 726-761,
+// 789-791, 941-961) in a Cornell-sized room: Rotate about X and Z (Lib.hs:763-787), three nested Translate / Rotate frames, Rotate
+// above a BVH, one-object makeBVH (BVHNode x x) in the world and in the light list, an XY rect among the lights (htblRandom /
+// htblPdfValue fallbacks, Lib.hs:684, 724), Metal fuzz > 1, a Perlin-textured medium in a rotated cuboid, a checker of a checker.
+SceneAndGen makeQuirksScene(Arena& A, Time t0, Time t1, RandGen gen, bool lit) {
+  Texture pertext = A.makePerlin(gen, 0.05);
+  Texture chk = A.CheckerTexture(A.CheckerTexture(A.ConstantColor(albedo(0.2, 0.3, 0.1)), A.ConstantColor(albedo(0.9, 0.9, 0.9))), pertext);
+  Material white = A.Lambertian(A.ConstantColor(albedo(0.73, 0.73, 0.73)));
+  Material red = A.Lambertian(A.ConstantColor(albedo(0.65, 0.05, 0.05)));
+  Material mirror = A.Metal(A.ConstantColor(albedo(0.8, 0.85, 0.9)), Fuzz{0.3});
+  Material fuzzy = A.Metal(A.ConstantColor(albedo(0.9, 0.6, 0.2)), Fuzz{2.0});
+  Material glass = A.Dielectric(RefractiveIdx{1.5});
+  Material light = A.DiffuseLight(A.ConstantColor(albedo(15, 15, 15)));
+  Material dim = A.DiffuseLight(A.ConstantColor(albedo(4, 4, 4)));
+  Hittable xzLight = A.rect(XZPlane, 163, 393, 177, 382, 554, light);
+  Hittable sphereLight = A.sphere(point3(460, 420, 120), 40, dim);
+  Hittable xyLight = A.rect(XYPlane, 100, 250, 350, 500, 554, dim);
+  std::vector<Hittable> cluster;
+  for (int i = 0; i < 12; ++i) {
+    const Vec3 p = randomVec3DoubleRM(gen, 0, 120);
+    const double r = randomDoubleRM(gen, 8, 20);
+    cluster.push_back(A.sphere(p, r, i % 3 == 0 ? glass : (i % 3 == 1 ? white : mirror)));
+  }
+  Hittable clusterBVH = A.makeBVH(gen, cluster);
+  Hittable lone = A.makeBVH(gen, {A.sphere(point3(90, 60, 380), 60, fuzzy)});
+  Material floorMat = A.Lambertian(chk);
+  std::vector<Hittable> objs = {
+      A.rect(YZPlane, 0, 555, 0, 555, 555, mirror), A.rect(YZPlane, 0, 555, 0, 555, 0, red), xzLight, sphereLight, xyLight,
+      A.rect(XZPlane, 0, 555, 0, 555, 0, floorMat), A.rect(XZPlane, 0, 555, 0, 555, 555, white), A.rect(XYPlane, 0, 555, 0, 555, 555, white),
+      A.translate(point3(360, 100, 260), A.rotate(XAxis, 25, A.cuboid(point3(-60, -60, -60), point3(60, 60, 60), white))),
+      A.translate(point3(200, 250, 250), A.rotate(ZAxis, -40, clusterBVH)),
+      A.rotate(XAxis, 10, A.translate(point3(420, 300, 300), A.rotate(ZAxis, 20, A.cuboid(point3(-40, -40, -40), point3(40, 40, 40), glass)))),
+      lone,
+      A.constantMedium(0.02, A.ConstantColor(albedo(0.9, 0.9, 0.9)), A.sphere(point3(140, 90, 150), 70, white)),
+      A.constantMedium(0.03, pertext, A.translate(point3(420, 80, 120), A.rotate(ZAxis, 30, A.cuboid(point3(-50, -50, -50), point3(50, 50, 50), white)))),
+      A.movingSphere(point3(280, 400, 300), point3(310, 430, 300), t0, t1, 35, A.Lambertian(A.ConstantColor(albedo(0.7, 0.3, 0.1))))};
+  Hittable world = A.makeBVH(gen, objs);
+  // lit: without the XY rect, whose (1,0,0) fallback direction makes the mixture pdf 0 on surfaces facing y or z (0/0)
+  Hittable lights = lit ? A.makeBVH(gen, {xzLight, sphereLight}) : A.makeBVH(gen, {xzLight, sphereLight, xyLight});
+  return done(world, lights, albedo(0, 0, 0), gen);
+}
+
 }  // namespace Scenes

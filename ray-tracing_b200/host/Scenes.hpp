@@ -25,5 +25,6 @@ SceneAndGen makeRandomSceneBookOne(Lib::Arena& A, Lib::RandGen gen, bool lit = f
 SceneAndGen makeRandomScene(Lib::Arena& A, Lib::Texture earthtex, Lib::Time t0, Lib::Time t1, Lib::RandGen gen, bool lit = false);
 SceneAndGen makeNextWeekFinalScene(Lib::Arena& A, Lib::Texture earthtex, Lib::Time t0, Lib::Time t1, Lib::RandGen gen, bool lit = false);
 SceneAndGen makeSyntheticScene(Lib::Arena& A, int n, Lib::RandGen gen);
+SceneAndGen makeQuirksScene(Lib::Arena& A, Lib::Time t0, Lib::Time t1, Lib::RandGen gen, bool lit = false);  // API-coverage scene, not in Scenes.hs
 
 }  // namespace Scenes

@@ -21,7 +21,7 @@ thread_local std::string g_err;
 
 Camera cameraFor(const std::string& n, int W, int H, int synthN) {
   std::pair<int, int> wh{W, H};
-  if (n == "cornell" || n == "cornell_smoke") return Scenes::cornellCamera(wh);
+  if (n == "cornell" || n == "cornell_smoke" || n == "quirks") return Scenes::cornellCamera(wh);
   if (n == "simple_light" || n == "earth" || n == "two_perlin" || n == "two_spheres") return Scenes::twoSpheresSceneCamera(wh);
   if (n == "random_book1" || n == "random") return Scenes::randomSceneCamera(wh);
   if (n == "next_week_final") return Scenes::nextWeekFinalSceneCamera(wh);
@@ -38,7 +38,7 @@ const char* rth_last_error() { return g_err.c_str(); }
 int rth_set_device_bvh(int min_objects) { const int old = (int)Arena::deviceBVHMin; Arena::deviceBVHMin = min_objects > 0 ? (size_t)min_objects : 0; return old; }
 double rth_last_device_bvh_ms() { return Arena::lastDeviceBVHms; }
 
-// names: cornell cornell_smoke simple_light earth two_perlin two_spheres random_book1 random next_week_final synthetic
+// names: cornell cornell_smoke simple_light earth two_perlin two_spheres random_book1 random next_week_final synthetic quirks
 void* rth_scene_create(const char* name, int64_t seed, double t0, double t1, const uint8_t* earth, int ew, int eh, int lit, int synthN) {
   try {
     auto h = std::make_unique<HostHandle>();
@@ -62,6 +62,7 @@ void* rth_scene_create(const char* name, int64_t seed, double t0, double t1, con
     else if (n == "random") sg = Scenes::makeRandomScene(A, earthTex(), t0, t1, gen, L);
     else if (n == "next_week_final") sg = Scenes::makeNextWeekFinalScene(A, earthTex(), t0, t1, gen, L);
     else if (n == "synthetic") sg = Scenes::makeSyntheticScene(A, synthN, gen);
+    else if (n == "quirks") sg = Scenes::makeQuirksScene(A, t0, t1, gen, L);
     else throw std::runtime_error("unknown scene: " + n);
     h->scene = sg.scene; h->g1 = sg.gen;
     return h.release();

@@ -1,0 +1,109 @@
+"""GPU parity on the API-coverage scene "quirks" (oracle/rt_scenes.hpp makeQuirksScene, host/Scenes.cpp makeQuirksScene): the
+combinations of the reference's constructors that none of its ten scenes uses but Lib.hs supports — Rotate about X and Z
+(Lib.hs:763-787), three nested Translate / Rotate frames, Rotate above a BVH, a one-object makeBVH (BVHNode x x, Lib.hs:948)
+in the world and in the light list, an XY rect among the lights (htblRandom -> (1,0,0), htblPdfValue -> 0: Lib.hs:684, 724),
+Metal fuzz > 1, a Perlin-textured ConstantMedium around a rotated cuboid, a checker whose children are a checker and a Perlin
+texture (Lib.hs:496-503).  Same bars as tests/test_gpu_parity.py, every call through the C ABI."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+W, H = 60, 40
+
+
+@pytest.fixture(scope="module")
+def quirks(gpu):
+    made = {}
+
+    def get(lit=False):
+        if lit not in made:
+            hs = gpu.HostScene("quirks", lit=lit)
+            made[lit] = (hs, hs.upload(W, H))
+        return made[lit][1]
+    yield get
+    for _, ds in made.values():
+        ds.destroy()
+
+
+def _rays(O, osc, n_rand=4000, seed=11):
+    cam = osc.camera(W, H)
+    prim = O.primary_rays(cam, W, H, time=0.4)
+    rng = np.random.default_rng(seed)
+    o = rng.random((n_rand, 3)) * 555.0  # origins anywhere in the room, also inside the media and the glass
+    d = rng.normal(size=(n_rand, 3))
+    d[:64, 1] = 0.0; d[:32, 2] = 0.0  # axis-parallel directions: zero divisors in the slab and rect tests
+    t = rng.random((n_rand, 1))
+    return np.concatenate([prim, np.concatenate([o, d, t], 1)], 0)
+
+
+@pytest.mark.parametrize("prec", ["f64", "f32", "mixed"])
+def test_quirks_trace(gpu, O, oracle_scene, quirks, prec):
+    """Visit order bit-exact on every ray (the two media draw inside `hit` and take log(xi): libm vs CUDA may move a medium's t
+    by an ulp on a few rays, nothing else may differ)."""
+    gp, op = {"f64": (gpu.PREC_F64, O.PREC_F64), "f32": (gpu.PREC_F32, O.PREC_F32), "mixed": (gpu.PREC_MIXED, O.PREC_MIXED)}[prec]
+    osc = oracle_scene("quirks")
+    rays = _rays(O, osc)
+    if prec != "f64":
+        rays = rays.astype(np.float32).astype(np.float64)
+    g = quirks().trace(rays, precision=gp, seed=9, log_stride=64)
+    o = osc.trace(rays, prec=op, seed=9, log_stride=64)
+    assert np.array_equal(g["nvisit"], o["nvisit"]) and np.array_equal(g["vhash"], o["vhash"]) and np.array_equal(g["vlog"], o["vlog"])
+    same = (g["hit"] == o["hit"]) & (g["prim"] == o["prim"]) & (g["rec"][:, 0] == o["rec"][:, 0]) & (g["front"] == o["front"])
+    assert same.mean() > (0.995 if prec == "f64" else 0.97), same.mean()
+    # rays whose closest hit is not a medium: everything bit-identical (t, p, normal use only + - * / sqrt)
+    solid = (o["prim"] >> 28) != 10
+    solid &= g["prim"] == o["prim"]
+    assert solid.sum() > 2000
+    assert np.array_equal(g["rec"][solid, :7], o["rec"][solid, :7]) and np.array_equal(g["mat"][solid], o["mat"][solid])
+    kinds = set(int(k) for k in np.unique(o["prim"][o["hit"] != 0] >> 28))
+    assert {1, 2, 3, 4, 5, 6, 10} <= kinds, kinds  # spheres, moving, all three rect planes, cuboids, media were all closest hits
+
+
+@pytest.mark.parametrize("lit", [False, True])
+def test_quirks_render_same_streams(gpu, O, oracle_scene, quirks, lit):
+    """fp32 kernels vs oracle<float> on identical per-(pixel,sample) streams.  HEAD light list: the XY rect's fallback direction
+    gives 0/0 on about half of the pixels, in the oracle as on the device (NaN masks must agree); lit: NaN-free."""
+    from test_gpu_parity import _cmp_images
+    spp = 8
+    img, st = quirks(lit).render(W, H, spp, depth=50, seed=21)
+    ref, _ = oracle_scene("quirks", lit).render(W, H, spp, depth=50, prec=O.PREC_F32, mode=1, seed=21)
+    assert st["samples"] == W * H * spp and st["launches"] == 1
+    if lit:
+        assert np.isfinite(img).all() and np.isfinite(ref).all()
+    else:
+        assert 0.2 < np.isnan(ref).any(axis=2).mean() < 0.8
+    _cmp_images(img, ref, frac_min=0.80, mean_tol=0.04)
+
+
+def test_quirks_render_fp64(gpu, O, oracle_scene, quirks):
+    """fp64 kernels vs oracle<double> (the reference's arithmetic), same streams."""
+    from test_gpu_parity import _cmp_images
+    img, _ = quirks(True).render(W, H, 4, depth=50, seed=33, precision=gpu.PREC_F64)
+    ref, _ = oracle_scene("quirks", True).render(W, H, 4, depth=50, prec=O.PREC_F64, mode=1, seed=33)
+    _cmp_images(img, ref, frac_min=0.85, mean_tol=0.03)
+
+
+def test_quirks_counters(gpu, O, oracle_scene, quirks):
+    """Reference-order traversal counts of the instrumented kernel = the oracle's (within the few paths that log(xi) separates)."""
+    _, st = quirks(True).render(W, H, 4, counted=True, seed=77)
+    _, os_ = oracle_scene("quirks", True).render(W, H, 4, prec=O.PREC_F32, mode=1, seed=77, stats=True)
+    c = st["counters"]
+    assert c["paths"] == os_["paths"] == W * H * 4
+    for k in ("bounces", "box_tests", "sphere_tests", "moving_tests", "rect_tests", "cuboid_tests", "translate_visits", "rotate_visits",
+              "medium_visits", "queries", "visits"):
+        assert os_[k] > 0 and abs(c[k] - os_[k]) <= 0.03 * os_[k] + 2, (k, c[k], os_[k])
+
+
+def test_quirks_nested_checker(gpu, O, oracle_scene, quirks):
+    """textureValue of the checker whose odd child is a checker and whose even child is the Perlin marble (recursive children)."""
+    hs = gpu.HostScene("quirks")
+    d = gpu.desc_arrays(hs.desc(W, H).contents)
+    chk = np.nonzero(d["tex_kind"] == 1)[0]
+    outer = int([t for t in chk if d["tex_kind"][d["tex_a"][t]] == 1 or d["tex_kind"][d["tex_b"][t]] == 1][0])
+    rng = np.random.default_rng(4)
+    q = np.concatenate([rng.random((4000, 2)), rng.random((4000, 3)) * 555.0], 1)
+    g = quirks().texture_value(outer, q, precision=gpu.PREC_F64)
+    o = oracle_scene("quirks").texture_value(outer, q, prec=O.PREC_F64)
+    assert (np.abs(g - o).max(axis=1) < 1e-9).mean() > 0.999
+    assert len(np.unique(np.round(o, 6), axis=0)) > 100  # the Perlin branch was taken, not only the two constants

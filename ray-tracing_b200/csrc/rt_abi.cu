@@ -41,6 +41,7 @@ struct HostScene {
   double background[3] = {0, 0, 0}, camera[24] = {0};
   std::vector<uint32_t> node_lsize, node_rsize;  // htblSize of the children (Lib.hs:662-671)
   int stackDepth = 1;
+  uint32_t lightCap = 0;  // entries of the light-pdf walk stack (rt_traverse.cuh)
 };
 
 template <class T> struct DevBuffers {
@@ -299,6 +300,7 @@ int renderLaunch(SceneEntry* e, const RtRenderParams& q, double* d_out, cudaStre
   a.rectMin = std::max(1u, tuneParam("RTB_RECT_MIN", hs.n_cuboids > hs.n_rects ? 6u : 3u));
   a.rareMin = std::max(1u, tuneParam("RTB_RARE_MIN", hs.n_media > 0 ? 4u : 8u));
   a.keepNode = std::max(1u, tuneParam("RTB_KEEP_NODE", 12)); a.keepLeaf = std::max(1u, tuneParam("RTB_KEEP_LEAF", 8));
+  a.lightCap = hs.lightCap;
   a.counter = e->d_counter; a.ctr = counted ? e->d_counter + 1 : nullptr; a.out = d_out;
   cudaError_t ce = (q.flags & RT_FLAG_FAST_MATH) ? launchRender<true>((int)q.precision, counted ? 1 : 0, dsc, a, e->hs.stackDepth, e->numSMs, st, gridOut)
                                                  : launchRender<false>((int)q.precision, counted ? 1 : 0, dsc, a, e->hs.stackDepth, e->numSMs, st, gridOut);
@@ -457,6 +459,7 @@ int rt_scene_create(const RtSceneDesc* d, int device, rt_scene_t* out) {
   if (media > 1) return fail(RT_ERR_UNSUPPORTED, "ConstantMedium nested inside a ConstantMedium boundary");
   if (lightDepth(h, h.lights_root) + 1 > kMaxLightDepth) return fail(RT_ERR_UNSUPPORTED, "lights BVH too deep");
   h.stackDepth = stackNeed;
+  h.lightCap = (h.lights_root >> 28) == K_BVH ? (uint32_t)lightDepth(h, h.lights_root) : 0u;  // DFS over L levels holds at most L entries
   h.node_lsize.resize(h.n_nodes); h.node_rsize.resize(h.n_nodes);
   for (uint32_t i = 0; i < h.n_nodes; ++i) { h.node_lsize[i] = (uint32_t)an.size[h.node_left[i]]; h.node_rsize[i] = (uint32_t)an.size[h.node_right[i]]; }
 

@@ -8,6 +8,9 @@
 //   textureKernel : textureValue probe.   tonemapKernel : albedoToColor.
 // Included by rt_launch_exact.cu (--fmad=false, FAST=false) and rt_launch_fast.cu (FAST=true).
 #pragma once
+#include <algorithm>
+#include <cstdlib>
+
 #include "rt_device.cuh"
 #include "rt_traverse.cuh"
 #include "rt_launch.h"
@@ -15,7 +18,10 @@
 namespace rtb {
 
 
-template <class T> struct MinBlocks { static constexpr int v = 6; };
+#ifndef RTB_MIN_BLOCKS
+#define RTB_MIN_BLOCKS 6  // resident 128-thread blocks per SM the fp32 render kernels are compiled for (80 registers)
+#endif
+template <class T> struct MinBlocks { static constexpr int v = RTB_MIN_BLOCKS; };
 template <> struct MinBlocks<double> { static constexpr int v = 1; };
 
 #include "rt_render_kernel.inl"
@@ -34,13 +40,14 @@ __global__ void textureKernel(const __grid_constant__ DScene<T> sc, uint32_t tex
 template <class T, class S, int INSTR, bool FAST>
 static cudaError_t launchRenderT(const DScene<T>& sc, const RenderArgs& a, int stackDepth, int numSMs, cudaStream_t st, int* gridOut) {
   auto kern = renderKernel<T, S, INSTR, FAST>;
-  size_t smem = (size_t)(stackDepth + extraWords<T>()) * kBlock * sizeof(uint32_t) + (kBlock / 32) * 16;  // columns + per-warp chunk slots
+  size_t smem = (size_t)columnWords<T>((uint32_t)stackDepth, a.lightCap) * kBlock * sizeof(uint32_t) + (kBlock / 32) * 16;  // columns + per-warp chunk slots
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   int perSM = 0;
   e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, kern, kBlock, smem);
   if (e != cudaSuccess) return e;
   if (perSM < 1) perSM = 1;
+  if (const char* v = std::getenv("RTB_BLOCKS_PER_SM")) perSM = std::max(1, std::min(perSM, std::atoi(v)));  // tuning experiments only
   int grid = numSMs * perSM;  // persistent: exactly one resident wave
   if (gridOut) *gridOut = grid;
   RenderArgs b = a; b.stackCap = (uint32_t)stackDepth;

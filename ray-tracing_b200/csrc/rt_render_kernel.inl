@@ -118,7 +118,7 @@ __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, Path
 // throughput (Lib.hs:1329-1333) and start the bounce's `hit world`.  Runs right after the traversal step that finished the query
 // (not through the shade class): the lane stays in the traversal classes.
 template <class T, int INSTR, bool FAST>
-RTB_D void lpdfAdvance(const DScene<T>& sc, Trav<T>& tr, PathState<T>& ps, Instr<INSTR>& ins) {
+RTB_D void lpdfAdvance(const DScene<T>& sc, Trav<T>& tr, PathState<T>& ps, Instr<INSTR>& ins, uint32_t lbase, uint32_t lightCap) {
   const uint32_t curLight = tr.xu(X_CURLIGHT);
   const T curW = xld<T>(tr, X_CURW);
   uint32_t lsp = tr.xu(X_LSP);
@@ -138,9 +138,11 @@ RTB_D void lpdfAdvance(const DScene<T>& sc, Trav<T>& tr, PathState<T>& ps, Instr
     } else if (lk == K_BVH) {
       const uint4 sz = __ldg(sc.node_sz + li);
       const uint32_t lc = bitsOf(ldq(sc.nodes + 2 * (size_t)li).w) & ~kPairBit, rc = bitsOf(ldq(sc.nodes + 2 * (size_t)li + 1).w);
-      if (lsp + 2 <= (uint32_t)kMaxLightDepth) {
-        tr.xu(X_LREF + (int)lsp) = rc; xst<T>(tr, X_LWT + (int)lsp, curW * ((T)sz.z / (T)sz.x)); ++lsp;
-        tr.xu(X_LREF + (int)lsp) = lc; xst<T>(tr, X_LWT + (int)lsp, curW * ((T)sz.y / (T)sz.x)); ++lsp;
+      if (lsp + 2 <= lightCap) {
+        uint32_t* e = lightEntry<T>(tr, lbase, lsp);
+        e[0] = rc; stT(e + tr.stride, tr.stride, curW * ((T)sz.z / (T)sz.x)); ++lsp;
+        e = lightEntry<T>(tr, lbase, lsp);
+        e[0] = lc; stT(e + tr.stride, tr.stride, curW * ((T)sz.y / (T)sz.x)); ++lsp;
       }
     }
   }
@@ -148,8 +150,10 @@ RTB_D void lpdfAdvance(const DScene<T>& sc, Trav<T>& tr, PathState<T>& ps, Instr
   uint32_t root;
   if (lsp > 0) {
     --lsp;
-    root = tr.xu(X_LREF + (int)lsp);
-    tr.xu(X_CURLIGHT) = root; xst<T>(tr, X_CURW, xld<T>(tr, X_LWT + (int)lsp)); tr.xu(X_LSP) = lsp;
+    const uint32_t* e = lightEntry<T>(tr, lbase, lsp);
+    root = e[0];
+    T wt; ldT(e + tr.stride, tr.stride, wt);
+    tr.xu(X_CURLIGHT) = root; xst<T>(tr, X_CURW, wt); tr.xu(X_LSP) = lsp;
   } else {
     const T pdfVal = (T)0.5 * (xld<T>(tr, X_LV1) + xld<T>(tr, X_LV2));
     ps.beta = scale(xld<T>(tr, X_LSPDF) / pdfVal, ps.beta);
@@ -179,7 +183,7 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
   ps.phase = PH_IDLE; ps.beta = mk<T>(1, 1, 1); ps.time = 0; ps.depthLeft = 0; ps.rng = Rng{0, 1};
   tr.xw(XW_ACCPIX) = kNone;
   // the warp's chunk of the path index space: {first pixel of the region, first sample, next offset, end offset}
-  volatile uint32_t* ws = smem + (size_t)(a.stackCap + extraWords<T>()) * blockDim.x + (threadIdx.x >> 5) * 4;
+  volatile uint32_t* ws = smem + (size_t)columnWords<T>(a.stackCap, a.lightCap) * blockDim.x + (threadIdx.x >> 5) * 4;
   if (lane == 0) { ws[0] = 0; ws[1] = 0; ws[2] = 0; ws[3] = 0; }
   __syncwarp();
   bool exhausted = false;
@@ -231,7 +235,7 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
       if (cls == 3) stepRare<T, INSTR, FAST>(sc, tr, ps.rng, ins);
     }
     if (pick != 4) {
-      if (ps.phase == PH_LPDF && tr.cur == kEmpty) lpdfAdvance<T, INSTR, FAST>(sc, tr, ps, ins);
+      if (ps.phase == PH_LPDF && tr.cur == kEmpty) lpdfAdvance<T, INSTR, FAST>(sc, tr, ps, ins, a.stackCap + (uint32_t)extraWords<T>(), a.lightCap);
     } else {
       // ---- shade class: (1) consume finished queries
       bool start = false; V3<T> qo = tr.o, qd = tr.d;

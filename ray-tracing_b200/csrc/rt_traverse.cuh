@@ -30,6 +30,7 @@ constexpr int kBlock = 128;               // threads per block of every kernel t
 //   words 0..5                      radiance accumulator of the current pixel (3 doubles), word 6 its pixel index
 //   words 8 + slot * w              "T slots" (w = sizeof(T)/4 words each; integers use the first word):
 //   words extraWords<T>() + [0, stackCap)   traversal stack
+//   words extraWords<T>() + stackCap + i * (1 + w)   light-pdf walk stack entry i: ref, weight (render kernel only)
 constexpr int XW_ACC = 0, XW_ACCPIX = 6, XW_TSLOTS = 8;
 constexpr int X_CHAIN = 0;      // ..3   open frames (transform refs)
 constexpr int X_BCHAIN = 4;     // ..7   frames of the best hit
@@ -37,10 +38,13 @@ constexpr int X_STMIN = 8, X_STBEST = 9, X_H1T = 10;   // outer query parked dur
 constexpr int X_WORLD = 11;     // ..16  world ray o,d saved while frames are open
 constexpr int X_LSPDF = 17, X_LV2 = 18, X_LV1 = 19, X_CURW = 20;  // Lambertian mixture-pdf bookkeeping (Lib.hs:367-382, 823-836)
 constexpr int X_CURLIGHT = 21, X_LSP = 22;
-constexpr int X_LREF = 23;      // ..30  htblPdfValue walk stack: refs
-constexpr int X_LWT = 31;       // ..38  ... and their weights
-constexpr int kTSlots = 39;
+constexpr int kTSlots = 23;
+// htblPdfValue's walk stack over the lights BVH (ref + weight per entry) sits BEHIND the traversal stack and is sized by the scene's
+// light list (RenderArgs::lightCap entries; none when the light list is not a BVH).  Columns are shared memory that the L1 does not
+// get: 16 words less per thread are 48 KB more L1 per SM at 6 blocks (cfg3: L1-bound node / leaf fetches, +15 % samples/s).
 template <class T> __host__ __device__ constexpr int extraWords() { return XW_TSLOTS + kTSlots * (int)(sizeof(T) / 4); }
+// words of one render-kernel column: fixed slots + traversal stack + light-pdf walk stack
+template <class T> __host__ __device__ constexpr uint32_t columnWords(uint32_t stackCap, uint32_t lightCap) { return (uint32_t)extraWords<T>() + stackCap + lightCap * (1u + (uint32_t)(sizeof(T) / 4)); }
 
 // Trav::flags bit fields
 constexpr uint32_t F_INSUB = 1u, F_SQHIT = 2u, F_QHIT = 4u, F_NANT = 8u;  // F_NANT: a NaN t was accepted (rect with d_k = 0, o_k = k)
@@ -77,6 +81,8 @@ RTB_D void ldT(const uint32_t* p, uint32_t stride, float& v) { v = __uint_as_flo
 RTB_D void ldT(const uint32_t* p, uint32_t stride, double& v) { v = __longlong_as_double((long long)((unsigned long long)p[0] | ((unsigned long long)p[stride] << 32))); }
 template <class T> RTB_D void xst(Trav<T>& tr, int slot, T v) { stT(&tr.xu(slot), tr.stride, v); }
 template <class T> RTB_D T xld(Trav<T>& tr, int slot) { T v; ldT(&tr.xu(slot), tr.stride, v); return v; }
+// entry i of the light-pdf walk stack; lbase = extraWords<T>() + stackCap (words)
+template <class T> RTB_D uint32_t* lightEntry(Trav<T>& tr, uint32_t lbase, uint32_t i) { return tr.col + (size_t)(lbase + i * (1u + (uint32_t)(sizeof(T) / 4))) * tr.stride; }
 
 RTB_D void axisMode(float d, bool oSafe, float& r, uint32_t& mode) {
   const float ad = fabsf(d);

@@ -9,7 +9,7 @@ name, spp = sys.argv[1], int(sys.argv[2])
 W, H = {"random": (600, 400), "random_book1": (600, 400), "cornell": (500, 500), "next_week_final": (400, 400)}.get(name, (400, 400))
 hs = pkg.HostScene(name); ds = hs.upload(W, H)
 ds.render(W, H, 4, seed=1)
-KN = ["RTB_SHADE_MIN", "RTB_KEEP_NODE", "RTB_KEEP_LEAF", "RTB_RECT_MIN", "RTB_RARE_MIN"]
+KN = ["RTB_SHADE_MIN", "RTB_KEEP_NODE", "RTB_KEEP_LEAF", "RTB_RECT_MIN", "RTB_RARE_MIN", "RTB_BLOCKS_PER_SM"]
 for setting in sys.argv[3:]:
     for k in KN: os.environ.pop(k, None)
     for kv in setting.split():

@@ -185,6 +185,11 @@ typedef struct RtLimits {
   uint32_t max_light_depth;  /* depth of the lights BVH walked by htblPdfValue */
 } RtLimits;
 
+/* Threading: every entry point may be called from any OS thread (Haskell `safe` foreign calls migrate).  Calls on ONE scene handle
+ * are serialised inside the library (they share the device copy of the scene, its work counter and its staging buffers); calls on
+ * different handles run concurrently.  A handle destroyed while another thread is inside a call on it stays valid until that call
+ * returns.  Asynchronous rt_render_device launches of one scene must be issued on ONE stream at a time (same work counter).
+ * rt_last_error() is thread-local. */
 typedef uint64_t rt_scene_t;
 
 int rt_abi_version(void);

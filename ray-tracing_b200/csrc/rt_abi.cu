@@ -52,6 +52,7 @@ template <class T> struct DevBuffers {
 };
 
 struct SceneEntry {
+  std::mutex mu;  // calls on one handle are serialised: they share the device scene, the work counter and the staging buffers
   HostScene hs;
   int device = 0, numSMs = 148;
   DevBuffers<float> f32;
@@ -67,7 +68,7 @@ struct SceneEntry {
 };
 
 std::mutex g_mu;
-std::map<uint64_t, std::unique_ptr<SceneEntry>> g_scenes;
+std::map<uint64_t, std::shared_ptr<SceneEntry>> g_scenes;
 uint64_t g_nextId = 1;
 
 template <class V, class P> void copyIn(V& dst, const P* src, size_t n) {
@@ -242,11 +243,20 @@ template <class T> int buildDevice(const HostScene& h, DevBuffers<T>& db) {
   return RT_OK;
 }
 
-SceneEntry* lookup(rt_scene_t id) {
+// the entry stays alive while a call holds the pointer, even if another thread destroys the handle meanwhile
+std::shared_ptr<SceneEntry> lookup(rt_scene_t id) {
   std::lock_guard<std::mutex> lk(g_mu);
   auto it = g_scenes.find(id);
-  return it == g_scenes.end() ? nullptr : it->second.get();
+  return it == g_scenes.end() ? nullptr : it->second;
 }
+
+// CUDA events that do not outlive an early error return
+struct Events {
+  cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+  int n = 0;
+  cudaError_t create(int count) { for (; n < count; ++n) { cudaError_t e = cudaEventCreate(&ev[n]); if (e != cudaSuccess) return e; } return cudaSuccess; }
+  ~Events() { for (int i = 0; i < n; ++i) cudaEventDestroy(ev[i]); }
+};
 
 int deviceScene(SceneEntry* e, uint32_t precision, const void** out) {
   int rc;
@@ -309,8 +319,10 @@ int renderLaunch(SceneEntry* e, const RtRenderParams& q, double* d_out, cudaStre
 }
 
 int renderHost(rt_scene_t scene, const RtRenderParams* params, double* out, RtStats* stats, bool counted) {
-  SceneEntry* e = lookup(scene);
-  if (!e) return fail(RT_ERR_HANDLE, "unknown scene handle");
+  const std::shared_ptr<SceneEntry> ep = lookup(scene);
+  if (!ep) return fail(RT_ERR_HANDLE, "unknown scene handle");
+  SceneEntry* e = ep.get();
+  std::lock_guard<std::mutex> lk(e->mu);
   if (!out) return fail(RT_ERR_ARG, "out_rgb_sum is null");
   RtRenderParams q;
   int rc = normaliseParams(params, q);
@@ -329,8 +341,9 @@ int renderHost(rt_scene_t scene, const RtRenderParams* params, double* out, RtSt
     CU(cudaHostAlloc(&e->h_fb, elems * sizeof(double), cudaHostAllocDefault));
     e->hfbElems = elems;
   }
-  cudaEvent_t e0, e1, e2;
-  CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1)); CU(cudaEventCreate(&e2));
+  Events evs;
+  CU(evs.create(3));
+  const cudaEvent_t e0 = evs.ev[0], e1 = evs.ev[1], e2 = evs.ev[2];
   CU(cudaMemsetAsync(e->d_fb, 0, elems * sizeof(double), 0));
   CU(cudaEventRecord(e0, 0));
   int grid = 0;
@@ -357,7 +370,6 @@ int renderHost(rt_scene_t scene, const RtRenderParams* params, double* out, RtSt
       for (int i = 0; i < 16; ++i) { stats->counters[i] = c[i + 1]; stats->sched[i] = c[i + 17]; }
     }
   }
-  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
   return RT_OK;
 }
 
@@ -397,7 +409,7 @@ int rt_scene_create(const RtSceneDesc* d, int device, rt_scene_t* out) {
   const uint32_t lim = kIdxMask;  // 27-bit indices: bit 27 of a ref is the pair mark
   if (d->n_nodes > lim || d->n_spheres > lim || d->n_moving > lim || d->n_rects > lim || d->n_cuboids > lim) return fail(RT_ERR_ARG, "too many objects");
 
-  auto e = std::make_unique<SceneEntry>();
+  auto e = std::make_shared<SceneEntry>();
   HostScene& h = e->hs;
   h.n_nodes = d->n_nodes; h.n_spheres = d->n_spheres; h.n_moving = d->n_moving; h.n_rects = d->n_rects; h.n_cuboids = d->n_cuboids;
   h.n_translates = d->n_translates; h.n_rotates = d->n_rotates; h.n_media = d->n_media; h.n_materials = d->n_materials; h.n_textures = d->n_textures;
@@ -482,7 +494,7 @@ int rt_scene_create(const RtSceneDesc* d, int device, rt_scene_t* out) {
 }
 
 int rt_scene_destroy(rt_scene_t scene) {
-  std::unique_ptr<SceneEntry> e;
+  std::shared_ptr<SceneEntry> e;
   {
     std::lock_guard<std::mutex> lk(g_mu);
     auto it = g_scenes.find(scene);
@@ -490,9 +502,12 @@ int rt_scene_destroy(rt_scene_t scene) {
     e = std::move(it->second);
     g_scenes.erase(it);
   }
-  cudaSetDevice(e->device);
-  cudaDeviceSynchronize();
-  e.reset();
+  {
+    std::lock_guard<std::mutex> lk(e->mu);  // a call in flight on another thread finishes first
+    cudaSetDevice(e->device);
+    cudaDeviceSynchronize();                // and so does asynchronous work of rt_render_device
+  }
+  e.reset();  // the buffers go with the last holder
   return RT_OK;
 }
 
@@ -500,16 +515,19 @@ int rt_render(rt_scene_t scene, const RtRenderParams* params, double* out, RtSta
 int rt_render_counted(rt_scene_t scene, const RtRenderParams* params, double* out, RtStats* stats) { return renderHost(scene, params, out, stats, true); }
 
 int rt_render_device(rt_scene_t scene, const RtRenderParams* params, double* d_out, void* cuda_stream, RtStats* stats) {
-  SceneEntry* e = lookup(scene);
-  if (!e) return fail(RT_ERR_HANDLE, "unknown scene handle");
+  const std::shared_ptr<SceneEntry> ep = lookup(scene);
+  if (!ep) return fail(RT_ERR_HANDLE, "unknown scene handle");
+  SceneEntry* e = ep.get();
+  std::lock_guard<std::mutex> lk(e->mu);
   if (!d_out) return fail(RT_ERR_ARG, "d_out_rgb_sum is null");
   RtRenderParams q;
   int rc = normaliseParams(params, q);
   if (rc) return rc;
   CU(cudaSetDevice(e->device));
   cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
-  cudaEvent_t e0 = nullptr, e1 = nullptr;
-  if (stats) { CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1)); CU(cudaEventRecord(e0, st)); }
+  Events evs;
+  if (stats) { CU(evs.create(2)); CU(cudaEventRecord(evs.ev[0], st)); }
+  const cudaEvent_t e0 = evs.ev[0], e1 = evs.ev[1];
   rc = renderLaunch(e, q, d_out, st, false, nullptr);
   if (rc) return rc;
   if (stats) {
@@ -518,15 +536,16 @@ int rt_render_device(rt_scene_t scene, const RtRenderParams* params, double* d_o
     std::memset(stats, 0, sizeof(*stats));
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
     stats->kernel_ms = ms; stats->samples = (uint64_t)(q.row1 - q.row0) * (q.col1 - q.col0) * q.sample_count; stats->launches = q.sample_count ? 1 : 0;
-    cudaEventDestroy(e0); cudaEventDestroy(e1);
   }
   return RT_OK;
 }
 
 int rt_trace(rt_scene_t scene, uint32_t precision, uint32_t flags, uint32_t n, const double* rays, double t_min, double t_max, uint64_t seed,
              uint32_t log_stride, int32_t* hit, double* rec, uint32_t* prim, uint32_t* mat, uint8_t* front, uint64_t* nvisit, uint64_t* vhash, uint32_t* vlog) {
-  SceneEntry* e = lookup(scene);
-  if (!e) return fail(RT_ERR_HANDLE, "unknown scene handle");
+  const std::shared_ptr<SceneEntry> ep = lookup(scene);
+  if (!ep) return fail(RT_ERR_HANDLE, "unknown scene handle");
+  SceneEntry* e = ep.get();
+  std::lock_guard<std::mutex> lk(e->mu);
   if (!rays && n) return fail(RT_ERR_ARG, "rays is null");
   if (n == 0) return RT_OK;
   CU(cudaSetDevice(e->device));
@@ -560,8 +579,10 @@ int rt_trace(rt_scene_t scene, uint32_t precision, uint32_t flags, uint32_t n, c
 }
 
 int rt_texture_value(rt_scene_t scene, uint32_t tex, uint32_t precision, uint32_t n, const double* q, double* out) {
-  SceneEntry* e = lookup(scene);
-  if (!e) return fail(RT_ERR_HANDLE, "unknown scene handle");
+  const std::shared_ptr<SceneEntry> ep = lookup(scene);
+  if (!ep) return fail(RT_ERR_HANDLE, "unknown scene handle");
+  SceneEntry* e = ep.get();
+  std::lock_guard<std::mutex> lk(e->mu);
   if (tex >= e->hs.n_textures) return fail(RT_ERR_ARG, "texture index out of range");
   if (n == 0) return RT_OK;
   if (!q || !out) return fail(RT_ERR_ARG, "q/out is null");

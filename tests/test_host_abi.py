@@ -160,3 +160,65 @@ def test_haskell_binding_matches_header():
     lib = ctypes.CDLL(os.path.join(ROOT, "ray-tracing_b200", "librt_b200.so"))
     for sym in re.findall(r'foreign import ccall \w+\s+"(\w+)"', s):
         assert hasattr(lib, sym), sym
+
+
+def _mini_desc(R, keep, **kw):
+    """A hand-written RtSceneDesc: one Lambertian material on a constant texture, one sphere; kw adds / overrides arrays
+    (numpy arrays are kept alive in `keep`)."""
+    f, u = np.float64, np.uint32
+    arrays = dict(sphere_cr=np.array([[0, 0, -1, 0.5]], f), sphere_mat=np.zeros(1, u), mat_kind=np.zeros(1, u), mat_tex=np.zeros(1, u),
+                  mat_param=np.zeros(1, f), tex_kind=np.zeros(1, u), tex_rgb=np.full((1, 3), 0.5, f), tex_a=np.zeros(1, u), tex_b=np.zeros(1, u),
+                  tex_scale=np.ones(1, f))
+    arrays.update({k: v for k, v in kw.items() if isinstance(v, np.ndarray)})
+    d = R.RtSceneDesc()
+    d.abi_version = 1
+    counts = dict(n_spheres="sphere_mat", n_materials="mat_kind", n_textures="tex_kind", n_nodes="node_left", n_translates="translate_child",
+                  n_rotates="rotate_child", n_media="medium_mat", n_rects="rect_mat", n_cuboids="cuboid_mat", n_moving="moving_mat")
+    for cnt, arr in counts.items():
+        setattr(d, cnt, len(arrays[arr]) if arr in arrays else 0)
+    for k, a in arrays.items():
+        a = np.ascontiguousarray(a); keep.append(a)
+        setattr(d, k, a.ctypes.data_as(C.c_void_p))
+    d.world_root = kw.get("world_root", (1 << 28) | 0)
+    d.lights_root = kw.get("lights_root", 0)  # Unhittable
+    return d
+
+
+def test_traversal_budget_limits_are_reported(R):
+    """Nesting beyond the compiled traversal budget (rt_get_limits) is RT_ERR_UNSUPPORTED (-2) with a message, decided on the host
+    before any device work; at the limit the description passes validation (and then stops at the missing device here)."""
+    L = R.core()
+    lim = R.RtLimits(); assert L.rt_get_limits(C.byref(lim)) == 0
+    assert lim.max_frames >= 4 and lim.max_stack >= 32 and lim.max_light_depth >= 4 and lim.max_medium_depth == 1
+    sid = C.c_uint64()
+    u, f = np.uint32, np.float64
+    SPH, BVH, TRN, MED = 1 << 28, 7 << 28, 8 << 28, 10 << 28
+
+    def create(**kw):
+        keep = []
+        rc = L.rt_scene_create(C.byref(_mini_desc(R, keep, **kw)), -1, C.byref(sid))
+        msg = L.rt_last_error().decode()
+        if rc == 0:
+            L.rt_scene_destroy(sid)
+        return rc, msg
+
+    def chain(n):  # translate i -> translate i+1 -> ... -> the sphere
+        return dict(translate_off=np.zeros((n, 3), f), translate_child=np.array([TRN | (i + 1) for i in range(n - 1)] + [SPH], u), world_root=TRN | 0)
+    rc, msg = create(**chain(int(lim.max_frames) + 1))
+    assert rc == -2 and "nested Translate/Rotate frames" in msg
+    rc, msg = create(**chain(int(lim.max_frames)))
+    assert rc in (0, -3), msg  # valid: created on a GPU box, "no CUDA device" here
+
+    # a medium whose boundary is a medium
+    rc, msg = create(medium_neg_inv_density=np.array([-100.0, -100.0], f), medium_mat=np.zeros(2, u), medium_boundary=np.array([MED | 1, SPH], u), world_root=MED | 0)
+    assert rc == -2 and "ConstantMedium nested" in msg
+
+    def left_chain(n):  # node i = (node i+1, sphere): a degenerate BVH of depth n
+        return dict(node_box=np.tile(np.array([-1, -1, -2, 1, 1, 0], f), (n, 1)), node_left=np.array([BVH | (i + 1) for i in range(n - 1)] + [SPH], u),
+                    node_right=np.full(n, SPH, u), node_size=np.arange(n + 1, 1, -1).astype(u))
+    rc, msg = create(**left_chain(int(lim.max_stack) + 4), world_root=BVH | 0)
+    assert rc == -2 and "traversal stack" in msg
+    rc, msg = create(**left_chain(int(lim.max_light_depth) + 2), world_root=SPH, lights_root=BVH | 0)
+    assert rc == -2 and "lights BVH too deep" in msg
+    rc, msg = create(**left_chain(3), world_root=BVH | 0, lights_root=BVH | 1)
+    assert rc in (0, -3), msg

@@ -297,10 +297,13 @@ int renderLaunch(SceneEntry* e, const RtRenderParams& q, double* d_out, cudaStre
   a.row0 = q.row0; a.row1 = q.row1; a.col0 = q.col0; a.col1 = q.col1;
   a.seed = q.seed;
   a.total_paths = (unsigned long long)(q.row1 - q.row0) * (q.col1 - q.col0) * q.sample_count;
-  // chunk: whole pixels where possible, ~1024 paths, at least 16 chunks per resident warp slot for balance
+  // chunk: ~1024 paths, halved until there are at least 8 chunks per warp slot for balance, down to 4 paths: launches with few, very
+  // long paths (the cfg5 sample: seconds per path) are tail-bound, and a warp that refills 4 lanes at a time keeps its lanes busier than
+  // one that waits for a 32-path chunk to drain (tools/chunk_probe.py: 90 k spheres, 480x270x1: 1424 -> 1242 ms; results are identical)
   unsigned long long warps = (unsigned long long)e->numSMs * 16ull;
   unsigned long long chunk = 1024;
-  while (chunk > 32 && a.total_paths / chunk < warps * 8ull) chunk /= 2;
+  const unsigned long long chunkMin = std::max(1u, tuneParam("RTB_CHUNK_MIN", 4));
+  while (chunk > chunkMin && a.total_paths / chunk < warps * 8ull) chunk /= 2;
   a.chunk = (uint32_t)chunk;
   // scheduler thresholds (rt_render_kernel.inl): single rects are cheap steps and worth running for 3 lanes, cuboid-heavy scenes batch
   // 6; media make the rare class frequent (3 rare steps per medium visit) and worth running for 4 lanes.  Measured on the

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 1
+#define RT_ABI_VERSION 2
 
 /* error codes */
 #define RT_OK 0
@@ -141,11 +141,17 @@ typedef struct RtSceneDesc {
 
 /* arithmetic of the device path */
 enum RtPrecision {
-  RT_PREC_F32 = 0,   /* fp32 everywhere (the production path) */
-  RT_PREC_MIXED = 1, /* fp32, sphere quadratic (Lib.hs:1091-1095) in fp64 */
+  RT_PREC_F32 = 0,   /* fp32 everywhere.  Opt-in: with t_min = 1e-4 (Lib.hs:77) an fp32 sphere quadratic re-hits a radius-1000
+                        sphere from its own surface, which biases every Book-1/2 scene against the reference's Double */
+  RT_PREC_MIXED = 1, /* THE PRODUCTION ARITHMETIC (what runRender and bench.py use): fp32, with the sphere quadratic
+                        (Lib.hs:1091-1095) in fp64 — meets the radiance bar against the reference's Double at the speed of F32 on B200 */
   RT_PREC_F64 = 2    /* fp64 everywhere: the reference's Double arithmetic, for validation */
 };
-#define RT_FLAG_FAST_MATH 1u /* allow FMA contraction, reciprocal slab test and fast transcendentals (not bit-exact vs the fp32 oracle) */
+#define RT_PREC_DEFAULT RT_PREC_MIXED
+#define RT_FLAG_FAST_MATH 1u   /* allow FMA contraction, reciprocal slab test and fast transcendentals (not bit-exact vs the fp32 oracle) */
+#define RT_FLAG_STRICT_MATH 2u /* parity instrument: sin / cos / atan2 / asin / log from the shared plain-arithmetic implementations
+                                  (ray-tracing_b200/csrc/rt_strict_math.h) instead of libdevice, so that a path is bit-identical to the
+                                  test oracle's; same kernels, same step and draw order.  Excludes RT_FLAG_FAST_MATH. */
 
 typedef struct RtRenderParams {
   uint32_t width, height;     /* full image size (imageWidth, imageHeight of mkRenderStaticEnv, Lib.hs:92-108) */
@@ -159,7 +165,10 @@ typedef struct RtRenderParams {
   uint32_t precision;         /* RtPrecision */
   uint32_t flags;             /* RT_FLAG_* */
   int32_t device;             /* CUDA device ordinal, -1 = current */
-  uint32_t reserved;
+  uint32_t n_gpus;            /* rt_render only: devices the call shards the frame over.  0 = the library default (1 until rt_init
+                                 changes it), k = devices 0..k-1 plus the scene's own.  The scene is replicated onto them on first use,
+                                 samples are split into contiguous slices (row bands when sample_count < devices), the partial
+                                 framebuffers are summed onto the scene's device over NVLink and copied to the host once. */
 } RtRenderParams;
 
 typedef struct RtStats {
@@ -171,7 +180,14 @@ typedef struct RtStats {
   uint64_t sched[16];      /* warp-scheduler statistics of the instrumented kernel: [0..4] iterations that ran class c (node, sphere,
                               rect, rare, shade), [5..9] lanes served by them, [10..14] lanes waiting per class summed over all
                               iterations, [15] iterations */
+  double reduce_ms;        /* multi-GPU rt_render: device time of the partial-framebuffer reduction onto the scene's device */
+  double replicate_ms;     /* multi-GPU rt_render: host time spent replicating the scene onto other devices in THIS call (0 once cached) */
+  uint32_t gpus;           /* devices that rendered a share of this call (1 for single-device calls) */
+  uint32_t reduce_kind;    /* RT_REDUCE_* actually used */
+  double gpu_kernel_ms[16];/* per device share: kernel time (kernel_ms is their maximum) */
 } RtStats;
+enum RtReduceKind { RT_REDUCE_NONE = 0, RT_REDUCE_PEER = 1 /* one kernel on the scene's device reading the peers' framebuffers over NVLink */,
+                    RT_REDUCE_NCCL = 2 /* ncclReduce(sum) onto the scene's device */, RT_REDUCE_STAGED = 3 /* no peer access: cudaMemcpyPeer + add */ };
 /* counters (algorithmic work, same definitions as the oracle's): */
 enum RtCounter { RT_CTR_PATHS = 0, RT_CTR_BOUNCES = 1, RT_CTR_BOX_TESTS = 2, RT_CTR_SPHERE_TESTS = 3, RT_CTR_MOVING_TESTS = 4,
                  RT_CTR_RECT_TESTS = 5, RT_CTR_CUBOID_TESTS = 6, RT_CTR_TRANSLATE = 7, RT_CTR_ROTATE = 8, RT_CTR_MEDIUM = 9,
@@ -183,6 +199,7 @@ typedef struct RtLimits {
   uint32_t max_frames;       /* nested Translate/Rotate frames above one primitive */
   uint32_t max_medium_depth; /* ConstantMedium inside a ConstantMedium boundary */
   uint32_t max_light_depth;  /* depth of the lights BVH walked by htblPdfValue */
+  uint32_t max_tex_depth;    /* nested CheckerTexture levels */
 } RtLimits;
 
 /* Threading: every entry point may be called from any OS thread (Haskell `safe` foreign calls migrate).  Calls on ONE scene handle
@@ -196,6 +213,14 @@ int rt_abi_version(void);
 const char* rt_last_error(void);
 int rt_device_count(void);             /* number of usable CUDA devices (0 if none) */
 int rt_get_limits(RtLimits* out);
+
+/* Multi-GPU set-up (optional).  The reference parallelises INSIDE its one pure entry point (runRender sparks, Lib.hs:1519-1520),
+ * so the drop-in shards inside rt_render: rt_init(n) makes n devices the default for every later rt_render whose params.n_gpus is 0
+ * (n = 0: all visible devices), enables peer access between them and, with RT_INIT_NCCL in flags, creates one NCCL communicator per
+ * device (ncclCommInitAll, libnccl.so.2 loaded at run time) so that the reduction is an ncclReduce instead of the library's own
+ * peer-memory kernel.  Returns the number of devices in use, or a negative error.  Without rt_init the library uses one device. */
+#define RT_INIT_NCCL 1u
+int rt_init(int n_gpus, uint32_t flags);
 
 /* Validates and uploads a scene to `device` (-1 = current).  Replaces nothing in the reference: it is the
  * receiving end of the flattener. */
@@ -228,8 +253,18 @@ int rt_trace(rt_scene_t scene, uint32_t precision, uint32_t flags, uint32_t n, c
              uint64_t seed, uint32_t log_stride, int32_t* hit, double* rec, uint32_t* prim, uint32_t* mat, uint8_t* front,
              uint64_t* nvisit, uint64_t* vhash, uint32_t* vlog);
 
-/* textureValue (Lib.hs:496-513) probe: q[n][5] = u v p.xyz -> out[n][3] */
-int rt_texture_value(rt_scene_t scene, uint32_t tex, uint32_t precision, uint32_t n, const double* q, double* out);
+/* Same as rt_render with a per-path log of the main queries (`hit world`, Lib.hs:1309) in bounce order: for path i (region pixels in
+ * row-major order, samples innermost) and bounce b < max_bounces, prim_log[i*max_bounces+b] = ref of the primitive hit (RT_NONE = miss,
+ * untouched entries are left as the caller initialised them) and t_log[...] = its t.  tools/parity_classify.py compares it with the
+ * oracle's log to find where and why a path separates.  Test instrument (slower kernel). */
+int rt_render_pathlog(rt_scene_t scene, const RtRenderParams* params, double* out_rgb_sum, uint32_t max_bounces, uint32_t* prim_log, double* t_log);
+
+/* textureValue (Lib.hs:496-513) probe: q[n][5] = u v p.xyz -> out[n][3]; flags: 0 or RT_FLAG_STRICT_MATH */
+int rt_texture_value(rt_scene_t scene, uint32_t tex, uint32_t precision, uint32_t flags, uint32_t n, const double* q, double* out);
+
+/* Device evaluation of the shared strict-math functions (fn: 0 sin, 1 cos, 2 atan2(x, y = second operand), 3 asin, 4 log) on host
+ * arrays x[n], y[n] -> out[n]; as_float != 0 evaluates the fp32 entry points.  For the host/device bit-identity test. */
+int rt_strict_math_eval(uint32_t fn, uint32_t n, const double* x, const double* y, double* out, int as_float);
 
 /* albedoToColor (Lib.hs:287-292) on the device: mean = sum / total_samples, sqrt, clamp [0,0.999], *256, floor.
  * in: host double[n] sums; out: host uint8[n].  NaN maps to 0 (GHC's floor NaN :: Word8 is platform-defined). */

@@ -48,6 +48,7 @@ type RtScene = Word64
 foreign import ccall unsafe "rt_abi_version"   c_rt_abi_version   :: IO CInt
 foreign import ccall unsafe "rt_last_error"    c_rt_last_error    :: IO CString
 foreign import ccall unsafe "rt_device_count"  c_rt_device_count  :: IO CInt
+foreign import ccall safe   "rt_init"          c_rt_init          :: CInt -> Word32 -> IO CInt
 -- `safe`: these block for milliseconds .. minutes and must not hold an RTS capability
 foreign import ccall safe   "rt_scene_create"  c_rt_scene_create  :: Ptr RtSceneDesc -> CInt -> Ptr RtScene -> IO CInt
 foreign import ccall safe   "rt_scene_destroy" c_rt_scene_destroy :: RtScene -> IO CInt
@@ -267,10 +268,15 @@ withSceneDesc (world, lights, Albedo bg) cam act = do
 -- The device RNG is counter-based -- sample s of pixel p draws from streamGen(seed, p, s) -- so one 64-bit seed taken from the
 -- first generator replaces the per-column generator chain of Lib.hs:1499-1523 (DESIGN.md section 3); pixel values are therefore
 -- not those of the CPU build sample for sample, they agree in distribution (tests/test_gpu_parity.py).
+-- NOINLINE: the unsafePerformIO body uploads a scene and renders; GHC must not duplicate or float it (ADVICE r1).
+{-# NOINLINE runRenderB200 #-}
 runRenderB200 :: RenderStaticEnv -> [RandGen] -> [VV.Vector RGB]
 runRenderB200 (RenderStaticEnv (scene, cam, (w, h), ns, depth, _numThreads, _)) gens = unsafePerformIO $ do
   ver <- c_rt_abi_version
   when (ver /= #{const RT_ABI_VERSION}) $ error "rt_b200: ABI version mismatch between rt_abi.h and librt_b200.so"
+  -- the reference parallelises inside runRender (sparks, Lib.hs:1519-1520): so does the drop-in -- every visible GPU renders a
+  -- slice of the samples and the partial frames are summed over NVLink inside rt_render (n_gpus = 0: the rt_init default)
+  _ <- c_rt_init 0 0
   let seed = case gens of
         (g : _) -> fst (randomWord64 g)
         []      -> error "runRender: no generators"
@@ -288,8 +294,9 @@ runRenderB200 (RenderStaticEnv (scene, cam, (w, h), ns, depth, _numThreads, _)) 
           #{poke RtRenderParams, total_samples} p (fromIntegral ns :: Word32)
           #{poke RtRenderParams, max_depth} p (fromIntegral depth :: Word32)
           #{poke RtRenderParams, seed} p (seed :: Word64)
-          #{poke RtRenderParams, precision} p (#{const RT_PREC_F32} :: Word32)
+          #{poke RtRenderParams, precision} p (#{const RT_PREC_DEFAULT} :: Word32)
           #{poke RtRenderParams, device} p (-1 :: Int32)
+          #{poke RtRenderParams, n_gpus} p (0 :: Word32)
           withForeignPtr sums $ \out -> c_rt_render sc p out nullPtr >>= check
   -- rt_render returns per-pixel radiance SUMS (double, row 0 = top); divide by ns and albedoToColor exactly as renderPos /
   -- runRender do (Lib.hs:1349, 287-292), so the 8-bit conversion -- NaN behaviour included -- stays the reference's own code

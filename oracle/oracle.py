@@ -22,7 +22,7 @@ STAT_NAMES = ["paths", "bounces", "box_tests", "sphere_tests", "moving_tests", "
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("oracle_capi.cpp", "rt_oracle.hpp", "rt_scenes.hpp")]
+    srcs = [os.path.join(_HERE, f) for f in ("oracle_capi.cpp", "rt_oracle.hpp", "rt_scenes.hpp", "../ray-tracing_b200/csrc/rt_strict_math.h")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "liboracle.so"], stdout=subprocess.DEVNULL)
     return so
@@ -40,9 +40,10 @@ def lib():
         L.orc_scene_roots.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_camera.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.orc_export.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
-        L.orc_trace.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_double, C.c_double, C.c_uint64, C.c_int] + [C.c_void_p] * 8
-        L.orc_render.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 7 + [C.c_uint64] + [C.c_int] * 5 + [C.c_void_p, C.c_void_p]
-        L.orc_texture_value.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_trace.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_double, C.c_double, C.c_uint64, C.c_int] + [C.c_void_p] * 8
+        L.orc_render.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 7 + [C.c_uint64] + [C.c_int] * 5 + [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32]
+        L.orc_texture_value.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_strict_math_eval.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.orc_splitmix.argtypes = [C.c_int64, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_stream.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_albedo_to_color.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
@@ -102,36 +103,57 @@ class OracleScene:
         assert got == n, (what, got, n)
         return d[:n], u[:n]
 
-    def trace(self, rays7, prec=PREC_F64, tmin=1e-4, tmax=np.inf, seed=0, log_stride=0):
+    def trace(self, rays7, prec=PREC_F64, tmin=1e-4, tmax=np.inf, seed=0, log_stride=0, strict=False):
         rays7 = np.ascontiguousarray(rays7, dtype=np.float64)
         n = rays7.shape[0]
         out = dict(hit=np.zeros(n, np.int32), rec=np.zeros((n, 9)), prim=np.zeros(n, np.uint32), mat=np.zeros(n, np.uint32),
                    front=np.zeros(n, np.uint8), nvisit=np.zeros(n, np.uint64), vhash=np.zeros(n, np.uint64),
                    vlog=np.zeros((n, max(log_stride, 1)), np.uint32))
-        rc = lib().orc_trace(self.h, prec, n, _p(rays7), tmin, tmax, seed, log_stride, _p(out["hit"]), _p(out["rec"]), _p(out["prim"]),
+        rc = lib().orc_trace(self.h, prec, 1 if strict else 0, n, _p(rays7), tmin, tmax, seed, log_stride, _p(out["hit"]), _p(out["rec"]), _p(out["prim"]),
                              _p(out["mat"]), _p(out["front"]), _p(out["nvisit"]), _p(out["vhash"]), _p(out["vlog"]))
         if rc:
             raise RuntimeError(lib().orc_last_error().decode())
         return out
 
-    def render(self, W, H, spp, depth=50, prec=PREC_F64, mode=1, seed=1, s0=0, region=None, threads=None, stats=False, cam=None):
-        """Returns (sum[H,W,3] float64 radiance sums, stats dict or None)."""
+    def render(self, W, H, spp, depth=50, prec=PREC_F64, mode=1, seed=1, s0=0, region=None, threads=None, stats=False, cam=None,
+               strict=False, order="reference", pathlog=0):
+        """Returns (sum[H,W,3] float64 radiance sums, stats dict or None) — or (sum, prim_log, t_log) with pathlog = max bounces.
+        strict: the shared strict-math functions (= the device under RT_FLAG_STRICT_MATH); order "beta": throughput accumulated
+        forward like the device (mode 1 only); both default to the reference's literal form."""
         cam = self.camera(W, H) if cam is None else np.ascontiguousarray(cam, dtype=np.float64)
         r0, r1, c0, c1 = region if region else (0, H, 0, W)
         threads = threads or os.cpu_count() or 1
         out = np.zeros((H, W, 3)); st = np.zeros(16, np.uint64)
-        rc = lib().orc_render(self.h, _p(cam), prec, W, H, s0, spp, depth, mode, seed, r0, r1, c0, c1, threads, _p(out), _p(st) if stats else None)
+        flags = (1 if strict else 0) | (2 if order == "beta" else 0)
+        if (flags or pathlog) and mode != 1:
+            raise ValueError("strict / beta / pathlog need mode=1")
+        prim = t = None
+        if pathlog:
+            paths = (r1 - r0) * (c1 - c0) * spp
+            prim = np.full((paths, pathlog), 0xFFFFFFFE, np.uint32); t = np.zeros((paths, pathlog))
+        rc = lib().orc_render(self.h, _p(cam), prec, W, H, s0, spp, depth, mode, seed, r0, r1, c0, c1, threads, _p(out), _p(st) if stats else None,
+                              flags, _p(prim) if pathlog else None, _p(t) if pathlog else None, pathlog)
         if rc:
             raise RuntimeError(lib().orc_last_error().decode())
+        if pathlog:
+            return out, prim, t
         return out, (dict(zip(STAT_NAMES, (int(x) for x in st))) if stats else None)
 
-    def texture_value(self, tex_id, q5, prec=PREC_F64):
+    def texture_value(self, tex_id, q5, prec=PREC_F64, strict=False):
         q5 = np.ascontiguousarray(q5, dtype=np.float64)
         out = np.zeros((q5.shape[0], 3))
-        rc = lib().orc_texture_value(self.h, tex_id, prec, q5.shape[0], _p(q5), _p(out))
+        rc = lib().orc_texture_value(self.h, tex_id, prec, 1 if strict else 0, q5.shape[0], _p(q5), _p(out))
         if rc:
             raise RuntimeError(lib().orc_last_error().decode())
         return out
+
+
+def strict_math_eval(fn, x, y=None, as_float=False):
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    y = np.zeros_like(x) if y is None else np.ascontiguousarray(y, dtype=np.float64)
+    out = np.zeros_like(x)
+    lib().orc_strict_math_eval(["sin", "cos", "atan2", "asin", "log"].index(fn), x.size, _p(x), _p(y), _p(out), int(as_float))
+    return out
 
 
 def splitmix(seed, n):

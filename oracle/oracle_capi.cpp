@@ -32,13 +32,17 @@ void statsOut(const Trace& t, uint64_t* s) {
 
 template <class T, class S>
 void traceImpl(const Scene& sc, int n, const double* rays, double tmin, double tmax, uint64_t seed, int logStride, int32_t* hitFlag,
-               double* rec, uint32_t* prim, uint32_t* mat, uint8_t* front, uint64_t* nvisit, uint64_t* vhash, uint32_t* vlog) {
-  for (int i = 0; i < n; ++i) {
+               double* rec, uint32_t* prim, uint32_t* mat, uint8_t* front, uint64_t* nvisit, uint64_t* vhash, uint32_t* vlog, bool strict) {
+  std::atomic<int> next{0};
+  auto work = [&]() {
+  for (;;) {
+    const int i = next.fetch_add(1);
+    if (i >= n) break;
     const double* r = rays + (size_t)i * 7;
     Ray<T> ray{Vec3<T>((T)r[0], (T)r[1], (T)r[2]), Vec3<T>((T)r[3], (T)r[4], (T)r[5]), (T)r[6]};
     SMGen g = streamGen(seed, (uint32_t)i, 0);
     Trace tr; tr.logVisits = logStride > 0;
-    Tracer<T, S> t(sc, g, &tr);
+    Tracer<T, S> t(sc, g, &tr, strict);
     Hit<T> h{};
     bool ok = t.hit(sc.world.get(), ray, (T)tmin, (T)tmax, h);
     hitFlag[i] = ok ? 1 : 0;
@@ -55,6 +59,12 @@ void traceImpl(const Scene& sc, int n, const double* rays, double tmin, double t
       for (int k = 0; k < logStride; ++k) vlog[(size_t)i * logStride + k] = k < (int)tr.visits.size() ? tr.visits[k] : 0xffffffffu;
     }
   }
+  };
+  const int nThreads = (int)std::max(1u, std::min(std::thread::hardware_concurrency(), (unsigned)((n + 63) / 64)));
+  std::vector<std::thread> th;
+  for (int k = 1; k < nThreads; ++k) th.emplace_back(work);
+  work();
+  for (auto& t : th) t.join();
 }
 }  // namespace
 
@@ -152,13 +162,15 @@ int orc_export(void* p, int what, double* d, uint32_t* u) {
 
 // K1 oracle: hit(world, ray, tmin, tmax) per ray; RNG for media = streamGen(seed, rayIndex, 0).
 // prec: 0 = <float,float>, 1 = <float,double> (mixed), 2 = <double,double> (the reference).
-int orc_trace(void* p, int prec, int n, const double* rays7, double tmin, double tmax, uint64_t seed, int logStride, int32_t* hitFlag,
+// flags: bit 0 = strict math (rt_strict_math.h), bit 1 = beta-order throughput (render only)
+int orc_trace(void* p, int prec, int flags, int n, const double* rays7, double tmin, double tmax, uint64_t seed, int logStride, int32_t* hitFlag,
               double* rec9, uint32_t* prim, uint32_t* mat, uint8_t* front, uint64_t* nvisit, uint64_t* vhash, uint32_t* vlog) {
   try {
     Scene& s = ((Handle*)p)->scene;
-    if (prec == 0) traceImpl<float, float>(s, n, rays7, tmin, tmax, seed, logStride, hitFlag, rec9, prim, mat, front, nvisit, vhash, vlog);
-    else if (prec == 1) traceImpl<float, double>(s, n, rays7, tmin, tmax, seed, logStride, hitFlag, rec9, prim, mat, front, nvisit, vhash, vlog);
-    else traceImpl<double, double>(s, n, rays7, tmin, tmax, seed, logStride, hitFlag, rec9, prim, mat, front, nvisit, vhash, vlog);
+    const bool strict = (flags & 1) != 0;
+    if (prec == 0) traceImpl<float, float>(s, n, rays7, tmin, tmax, seed, logStride, hitFlag, rec9, prim, mat, front, nvisit, vhash, vlog, strict);
+    else if (prec == 1) traceImpl<float, double>(s, n, rays7, tmin, tmax, seed, logStride, hitFlag, rec9, prim, mat, front, nvisit, vhash, vlog, strict);
+    else traceImpl<double, double>(s, n, rays7, tmin, tmax, seed, logStride, hitFlag, rec9, prim, mat, front, nvisit, vhash, vlog, strict);
     return 0;
   } catch (const std::exception& e) { g_err = e.what(); return -1; }
 }
@@ -166,8 +178,9 @@ int orc_trace(void* p, int prec, int n, const double* rays7, double tmin, double
 // mode 0: reference RNG plumbing (runRender, per-column SplitMix; `seed` stands in for Main's entropy);
 // mode 1: per-(pixel,sample) streams (the product's RNG), region/sample-range restricted.
 // out: double[H*W*3] radiance SUMS, row 0 = top.  stats16 may be null.
+// flags / path log (mode 1 only): see orc_trace; pathPrim / pathT: [paths][pathStride] or null
 int orc_render(void* p, const double* cam24, int prec, int W, int H, int s0, int ns, int maxDepth, int mode, uint64_t seed, int row0, int row1,
-               int col0, int col1, int nThreads, double* out, uint64_t* stats16) {
+               int col0, int col1, int nThreads, double* out, uint64_t* stats16, int flags, uint32_t* pathPrim, double* pathT, uint32_t pathStride) {
   try {
     Scene& s = ((Handle*)p)->scene;
     Camera cam = cameraFrom24(cam24);
@@ -178,9 +191,10 @@ int orc_render(void* p, const double* cam24, int prec, int W, int H, int s0, int
       else if (prec == 1) r = renderReference<float, double>(s, cam, W, H, ns, maxDepth, seed, nThreads, st);
       else r = renderReference<double, double>(s, cam, W, H, ns, maxDepth, seed, nThreads, st);
     } else {
-      if (prec == 0) r = renderStreams<float, float>(s, cam, W, H, s0, ns, maxDepth, seed, row0, row1, col0, col1, nThreads, st);
-      else if (prec == 1) r = renderStreams<float, double>(s, cam, W, H, s0, ns, maxDepth, seed, row0, row1, col0, col1, nThreads, st);
-      else r = renderStreams<double, double>(s, cam, W, H, s0, ns, maxDepth, seed, row0, row1, col0, col1, nThreads, st);
+      const bool strict = (flags & 1) != 0, beta = (flags & 2) != 0;
+      if (prec == 0) r = renderStreams<float, float>(s, cam, W, H, s0, ns, maxDepth, seed, row0, row1, col0, col1, nThreads, st, strict, beta, pathPrim, pathT, pathStride);
+      else if (prec == 1) r = renderStreams<float, double>(s, cam, W, H, s0, ns, maxDepth, seed, row0, row1, col0, col1, nThreads, st, strict, beta, pathPrim, pathT, pathStride);
+      else r = renderStreams<double, double>(s, cam, W, H, s0, ns, maxDepth, seed, row0, row1, col0, col1, nThreads, st, strict, beta, pathPrim, pathT, pathStride);
     }
     std::memcpy(out, r.sum.data(), r.sum.size() * sizeof(double));
     statsOut(r.stats, stats16);
@@ -189,23 +203,37 @@ int orc_render(void* p, const double* cam24, int prec, int W, int H, int s0, int
 }
 
 // textureValue probe (Lib.hs:496-513): q = n x (u, v, px, py, pz) -> out n x 3
-int orc_texture_value(void* p, int texId, int prec, int n, const double* q, double* out) {
+int orc_texture_value(void* p, int texId, int prec, int flags, int n, const double* q, double* out) {
+  const bool strict = (flags & 1) != 0;
   Scene& s = ((Handle*)p)->scene;
   if (texId < 0 || texId >= (int)s.texs.size()) { g_err = "bad texture id"; return -1; }
   SMGen g{0, 1};
   for (int i = 0; i < n; ++i) {
     const double* a = q + (size_t)i * 5;
     if (prec == 2) {
-      Tracer<double, double> t(s, g, nullptr);
+      Tracer<double, double> t(s, g, nullptr, strict);
       auto c = t.textureValue(s.texs[texId], a[0], a[1], Vec3<double>(a[2], a[3], a[4]));
       out[i * 3] = c.x; out[i * 3 + 1] = c.y; out[i * 3 + 2] = c.z;
     } else {
-      Tracer<float, float> t(s, g, nullptr);
+      Tracer<float, float> t(s, g, nullptr, strict);
       auto c = t.textureValue(s.texs[texId], (float)a[0], (float)a[1], Vec3<float>((float)a[2], (float)a[3], (float)a[4]));
       out[i * 3] = c.x; out[i * 3 + 1] = c.y; out[i * 3 + 2] = c.z;
     }
   }
   return 0;
+}
+
+// the shared strict-math functions on the host (fn: 0 sin 1 cos 2 atan2(x, y) 3 asin 4 log) for the host/device identity test
+void orc_strict_math_eval(int fn, int n, const double* x, const double* y, double* out, int asFloat) {
+  for (int i = 0; i < n; ++i) {
+    if (asFloat) {
+      const float a = (float)x[i], b = (float)y[i];
+      out[i] = fn == 0 ? rtb_strict::sinS(a) : fn == 1 ? rtb_strict::cosS(a) : fn == 2 ? rtb_strict::atan2S(a, b) : fn == 3 ? rtb_strict::asinS(a) : rtb_strict::logS(a);
+    } else {
+      const double a = x[i], b = y[i];
+      out[i] = fn == 0 ? rtb_strict::sinS(a) : fn == 1 ? rtb_strict::cosS(a) : fn == 2 ? rtb_strict::atan2S(a, b) : fn == 3 ? rtb_strict::asinS(a) : rtb_strict::logS(a);
+    }
+  }
 }
 
 // RNG known-answer helpers

@@ -29,6 +29,9 @@
 #include <thread>
 #include <vector>
 
+// the product's shared strict-math header (test infrastructure may depend on the product, never the other way round)
+#include "../ray-tracing_b200/csrc/rt_strict_math.h"
+
 namespace orc {
 
 // =====================================================================================================
@@ -403,6 +406,10 @@ struct Trace {
   uint64_t nVisit = 0, visitHash = 0xcbf29ce484222325ULL;
   // counters (BASELINE.md "algorithmic work"): box tests, primitive tests by kind, sphere hit records, bounces
   uint64_t boxTests = 0, prim[Hittable::NKinds] = {0}, sphereHits = 0, bounces = 0, paths = 0, noiseCalls = 0, texels = 0, queries = 0;
+  // per-path log of the main queries (rayColor's `hit world`), bounce order: (prim ref | 0xffffffff = miss, t) — same definition as
+  // the device's rt_render_pathlog; filled when pathPrim != nullptr
+  uint32_t* pathPrim = nullptr; double* pathT = nullptr; uint32_t pathStride = 0, pathBounce = 0;
+  inline void bounce(uint32_t prim, double t) { if (pathPrim) { if (pathBounce < pathStride) { pathPrim[pathBounce] = prim; pathT[pathBounce] = t; } ++pathBounce; } }
   inline void visit(const Hittable* h) {
     uint32_t r = refOf(h);
     ++nVisit; visitHash = (visitHash ^ r) * 0x100000001b3ULL;
@@ -438,7 +445,16 @@ template <class T> inline bool boxRayIntersect(const Box& b, const Ray<T>& r, T 
 
 template <class T, class S> struct Tracer {
   const Scene& sc; SMGen& g; Trace* tr;
-  Tracer(const Scene& s, SMGen& gen, Trace* t) : sc(s), g(gen), tr(t) {}
+  // strict: sin / cos / atan2 / asin / log from the shared plain-arithmetic header (bit-identical to the device under
+  // RT_FLAG_STRICT_MATH) and schlick's fifth power as products; betaOrder: throughput accumulated forward (the device's order)
+  // instead of the reference's multiply-on-return chain (Lib.hs:1321-1333).  Both default to the reference's literal form.
+  bool strict = false, betaOrder = false;
+  Tracer(const Scene& s, SMGen& gen, Trace* t, bool strictMath = false, bool beta = false) : sc(s), g(gen), tr(t), strict(strictMath), betaOrder(beta) {}
+  T msin(T x) const { return strict ? rtb_strict::sinS(x) : std::sin(x); }
+  T mcos(T x) const { return strict ? rtb_strict::cosS(x) : std::cos(x); }
+  T matan2(T y, T x) const { return strict ? rtb_strict::atan2S(y, x) : std::atan2(y, x); }
+  T masin(T x) const { return strict ? rtb_strict::asinS(x) : std::asin(x); }
+  T mlog(T x) const { return strict ? rtb_strict::logS(x) : std::log(x); }
 
   // ---- rectHit (Lib.hs:1005-1028) ; plane: 0 XY (i=x,j=y,k=z) 1 XZ (i=x,j=z,k=y) 2 YZ (i=y,j=z,k=x)
   bool rectHit(int plane, T i0, T i1, T j0, T j1, T k, const Material* mat, uint32_t prim, const Ray<T>& r, T t_min, T t_max, Hit<T>& out) {
@@ -481,8 +497,8 @@ template <class T, class S> struct Tracer {
       Vec3<T> pShift = p - scT;
       Vec3<T> outward = divide(pShift, srT);
       faceNormal(r, outward, out.frontFace, out.normal);
-      T phi = std::atan2(outward.z, outward.x);
-      T theta = std::asin(outward.y);
+      T phi = matan2(outward.z, outward.x);
+      T theta = masin(outward.y);
       out.u = (T)1.0 - ((phi + K<T>::pi()) / ((T)2 * K<T>::pi()));
       out.v = (theta + (K<T>::pi() / (T)2)) / K<T>::pi();
       out.t = t; out.p = p; out.mat = mat; out.prim = prim;
@@ -555,7 +571,7 @@ template <class T, class S> struct Tracer {
         T rayLength = length(r.d);
         T distInsideBound = (rec2t - rec1t) * rayLength;
         T rnd = nextReal<T>(g);
-        T hitDist = (T)h->nInvD * std::log(rnd);
+        T hitDist = (T)h->nInvD * mlog(rnd);
         if (hitDist > distInsideBound) return false;
         T newt = rec1t + (hitDist / rayLength);
         out.t = newt; out.p = at(r, newt); out.normal = Vec3<T>(1, 0, 0); out.u = 0; out.v = 0; out.frontFace = true;
@@ -583,11 +599,11 @@ template <class T, class S> struct Tracer {
   }
   Vec3<T> randomUnitVector() {  // 1187-1197
     T aa = rnd(); T a = aa * 2 * K<T>::pi(); T zz = rnd(); T z = (zz * 2) - 1; T r = std::sqrt(1 - z * z);
-    return Vec3<T>(r * std::cos(a), r * std::sin(a), z);
+    return Vec3<T>(r * mcos(a), r * msin(a), z);
   }
   Vec3<T> randomCosineDirection() {  // 1206-1217
     T r1 = rnd(), r2 = rnd(); T z = std::sqrt(1 - r2); T phi = 2 * K<T>::pi() * r1;
-    T x = std::cos(phi) * std::sqrt(r2); T y = std::sin(phi) * std::sqrt(r2);
+    T x = mcos(phi) * std::sqrt(r2); T y = msin(phi) * std::sqrt(r2);
     return Vec3<T>(x, y, z);
   }
   Vec3<T> randomToSphere(T radius, T distSquared) {  // 1219-1228
@@ -595,7 +611,7 @@ template <class T, class S> struct Tracer {
     T z = 1 + r2 * (std::sqrt(1 - radius * radius / distSquared) - 1);
     T phi = 2 * K<T>::pi() * r1;
     T om = std::sqrt(1 - z * z);
-    return Vec3<T>(std::cos(phi) * om, std::sin(phi) * om, z);
+    return Vec3<T>(mcos(phi) * om, msin(phi) * om, z);
   }
 
   // ---- textures (Lib.hs:441-513)
@@ -628,10 +644,10 @@ template <class T, class S> struct Tracer {
     switch (tex->kind) {
       case Texture::Constant: return Vec3<T>((T)tex->rgb[0], (T)tex->rgb[1], (T)tex->rgb[2]);
       case Texture::Checker:
-        if (std::sin(10 * p.x) * std::sin(10 * p.y) * std::sin(10 * p.z) < 0) return textureValue(tex->odd.get(), u, v, p);
+        if (msin(10 * p.x) * msin(10 * p.y) * msin(10 * p.z) < 0) return textureValue(tex->odd.get(), u, v, p);
         return textureValue(tex->even.get(), u, v, p);
       case Texture::Perlin: {
-        T m = (T)0.5 * ((T)1.0 + std::sin(p.z + 10 * turb(tex, p, 7)));  // marbleTexture 512-513
+        T m = (T)0.5 * ((T)1.0 + msin(p.z + 10 * turb(tex, p, 7)));  // marbleTexture 512-513
         return scale(m, Vec3<T>(1, 1, 1));
       }
       default: {
@@ -707,9 +723,10 @@ template <class T, class S> struct Tracer {
     Vec3<T> rOutPerp = scale(-std::sqrt((T)1.0 - squaredLength(rOutParallel)), n);
     return rOutParallel + rOutPerp;
   }
-  static T schlick(T cosine, T ref_idx) {  // 899-903
+  T schlick(T cosine, T ref_idx) const {  // 899-903
     T r0 = ((T)1.0 - ref_idx) / ((T)1.0 + ref_idx);
     T r1 = r0 * r0;
+    if (strict) { T x = (T)1 - cosine; T x2 = x * x; return r1 + ((T)1.0 - r1) * ((x2 * x2) * x); }  // the device's form of `**5`
     return r1 + ((T)1.0 - r1) * std::pow((T)1 - cosine, (T)5);
   }
   struct ScatterRecord { Ray<T> ray; bool specular; Vec3<T> att; T pdf; };  // 819
@@ -771,17 +788,43 @@ template <class T, class S> struct Tracer {
 
   // ---- rayColor (Lib.hs:1298-1333): plain recursion == the CPS closure chain, same draw and multiply order
   Vec3<T> rayColor(const Ray<T>& r, int d) {
+    if (betaOrder) return rayColorBeta(r, d);
     if (d <= 0) return Vec3<T>(0, 0, 0);
     Hit<T> h;
     if (tr) { ++tr->queries; ++tr->bounces; }
-    if (!hit(sc.world.get(), r, K<T>::epsilon(), K<T>::infinity(), h))
+    if (!hit(sc.world.get(), r, K<T>::epsilon(), K<T>::infinity(), h)) {
+      if (tr) tr->bounce(0xffffffffu, 0.0);
       return Vec3<T>((T)sc.background[0], (T)sc.background[1], (T)sc.background[2]);
+    }
+    if (tr) tr->bounce(h.prim, (double)h.t);
     ScatterRecord s;
     if (!scatter(h.mat, r, h, s)) return emitted(h.mat, h);
     if (s.specular) return s.att * rayColor(s.ray, d - 1);
     T spdf = scatteringPdf(h, s.ray);
     Vec3<T> nw = rayColor(s.ray, d - 1);
     return s.att * scale(spdf, divide(nw, s.pdf));
+  }
+
+  // The same path with the throughput accumulated FORWARD, beta <- beta (x) att [* spdf / pdf], L = beta (x) terminal: the order the
+  // device multiplies in (it cannot hold 50 pending frames per lane).  Identical draws, hits and decisions; only the rounding of the
+  // final product differs from rayColor (tests/test_oracle.py bounds the difference).  Not in the reference.
+  Vec3<T> rayColorBeta(Ray<T> r, int d) {
+    Vec3<T> beta(1, 1, 1);
+    for (;;) {
+      if (d <= 0) return beta * Vec3<T>(0, 0, 0);
+      Hit<T> h;
+      if (tr) { ++tr->queries; ++tr->bounces; }
+      if (!hit(sc.world.get(), r, K<T>::epsilon(), K<T>::infinity(), h)) {
+        if (tr) tr->bounce(0xffffffffu, 0.0);
+        return beta * Vec3<T>((T)sc.background[0], (T)sc.background[1], (T)sc.background[2]);
+      }
+      if (tr) tr->bounce(h.prim, (double)h.t);
+      ScatterRecord s;
+      if (!scatter(h.mat, r, h, s)) return beta * emitted(h.mat, h);
+      if (s.specular) { if (h.mat->kind != Material::Dielectric) beta = beta * s.att; }  // Dielectric: att = (1,1,1)
+      else { T spdf = scatteringPdf(h, s.ray); beta = scale(spdf / s.pdf, beta * s.att); }
+      r = s.ray; --d;
+    }
   }
 
   // ---- getRay (Lib.hs:1253-1267)
@@ -845,12 +888,13 @@ inline RenderOut renderReference(const Scene& sc, const Camera& cam, int W, int 
 // region: rows [row0,row1) x cols [col0,col1) of the full WxH image; samples [s0, s0+ns)
 template <class T, class S>
 inline RenderOut renderStreams(const Scene& sc, const Camera& cam, int W, int H, int s0, int ns, int maxDepth, uint64_t seed,
-                               int row0, int row1, int col0, int col1, int nThreads, bool stats) {
+                               int row0, int row1, int col0, int col1, int nThreads, bool stats, bool strict = false, bool betaOrder = false,
+                               uint32_t* pathPrim = nullptr, double* pathT = nullptr, uint32_t pathStride = 0) {
   RenderOut out; out.sum.assign((size_t)W * H * 3, 0.0);
   std::vector<Trace> traces(std::max(1, nThreads));
   std::atomic<int> nextRow{row0};
   auto work = [&](int tid) {
-    Trace* tr = stats ? &traces[tid] : nullptr;
+    Trace* tr = (stats || pathPrim) ? &traces[tid] : nullptr;
     for (;;) {
       int row = nextRow.fetch_add(1); if (row >= row1) break;
       int y = H - 1 - row;
@@ -859,7 +903,11 @@ inline RenderOut renderStreams(const Scene& sc, const Camera& cam, int W, int H,
         double acc[3] = {0, 0, 0};
         for (int s = s0; s < s0 + ns; ++s) {
           SMGen g = streamGen(seed, pixel, (uint32_t)s);
-          Tracer<T, S> t(sc, g, tr);
+          Tracer<T, S> t(sc, g, tr, strict, betaOrder);
+          if (pathPrim) {  // path index: region pixels row-major, samples innermost (the device's rt_render_pathlog order)
+            const size_t path = ((size_t)(row - row0) * (col1 - col0) + (x - col0)) * ns + (s - s0);
+            tr->pathPrim = pathPrim + path * pathStride; tr->pathT = pathT + path * pathStride; tr->pathStride = pathStride; tr->pathBounce = 0;
+          }
           T ru = nextReal<T>(g); T rv = nextReal<T>(g);
           T u = ((T)x + ru) / (T)W, v = ((T)y + rv) / (T)H;
           Ray<T> r = t.getRay(cam, u, v);

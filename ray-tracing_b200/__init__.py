@@ -16,7 +16,11 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
 
 PREC_F32, PREC_MIXED, PREC_F64 = 0, 1, 2
+PREC_DEFAULT = PREC_MIXED  # RT_PREC_DEFAULT: the production arithmetic (include/rt_abi.h)
 FLAG_FAST_MATH = 1
+FLAG_STRICT_MATH = 2
+INIT_NCCL = 1
+REDUCE_KINDS = ["none", "peer-kernel", "nccl", "staged"]
 RT_NONE = 0xFFFFFFFF
 KIND_NAMES = ["Unhittable", "Sphere", "MovingSphere", "RectXY", "RectXZ", "RectYZ", "Cuboid", "BVHNode", "Translate",
               "Rotate", "ConstantMedium"]
@@ -51,21 +55,24 @@ class RtRenderParams(C.Structure):
     _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("sample_offset", C.c_uint32), ("sample_count", C.c_uint32),
                 ("total_samples", C.c_uint32), ("max_depth", C.c_uint32), ("row0", C.c_uint32), ("row1", C.c_uint32),
                 ("col0", C.c_uint32), ("col1", C.c_uint32), ("seed", C.c_uint64), ("precision", C.c_uint32),
-                ("flags", C.c_uint32), ("device", C.c_int32), ("reserved", C.c_uint32)]
+                ("flags", C.c_uint32), ("device", C.c_int32), ("n_gpus", C.c_uint32)]
 
 
 class RtStats(C.Structure):
     _fields_ = [("kernel_ms", C.c_double), ("h2d_ms", C.c_double), ("d2h_ms", C.c_double), ("samples", C.c_uint64),
-                ("launches", C.c_uint64), ("counters", C.c_uint64 * 16), ("sched", C.c_uint64 * 16)]
+                ("launches", C.c_uint64), ("counters", C.c_uint64 * 16), ("sched", C.c_uint64 * 16),
+                ("reduce_ms", C.c_double), ("replicate_ms", C.c_double), ("gpus", C.c_uint32), ("reduce_kind", C.c_uint32),
+                ("gpu_kernel_ms", C.c_double * 16)]
 
 
 class RtLimits(C.Structure):
     _fields_ = [("max_stack", C.c_uint32), ("max_frames", C.c_uint32), ("max_medium_depth", C.c_uint32),
-                ("max_light_depth", C.c_uint32)]
+                ("max_light_depth", C.c_uint32), ("max_tex_depth", C.c_uint32)]
 
 
-ABI_SYMBOLS = ["rt_abi_version", "rt_last_error", "rt_device_count", "rt_get_limits", "rt_scene_create", "rt_scene_destroy",
-               "rt_render", "rt_render_device", "rt_render_counted", "rt_trace", "rt_texture_value", "rt_tonemap", "rt_selftest_division", "rt_bvh_node_count", "rt_bvh_build", "rt_shutdown"]
+ABI_SYMBOLS = ["rt_abi_version", "rt_last_error", "rt_device_count", "rt_get_limits", "rt_init", "rt_scene_create", "rt_scene_destroy",
+               "rt_render", "rt_render_device", "rt_render_counted", "rt_render_pathlog", "rt_trace", "rt_texture_value", "rt_tonemap",
+               "rt_selftest_division", "rt_strict_math_eval", "rt_bvh_node_count", "rt_bvh_build", "rt_shutdown"]
 
 _core = None
 _host = None
@@ -95,7 +102,10 @@ def core():
         L.rt_render_device.argtypes = [C.c_uint64, C.POINTER(RtRenderParams), C.c_void_p, C.c_void_p, C.POINTER(RtStats)]
         L.rt_trace.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_double, C.c_double, C.c_uint64,
                                C.c_uint32] + [C.c_void_p] * 8
-        L.rt_texture_value.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
+        L.rt_texture_value.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
+        L.rt_init.argtypes = [C.c_int, C.c_uint32]
+        L.rt_render_pathlog.argtypes = [C.c_uint64, C.POINTER(RtRenderParams), C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
+        L.rt_strict_math_eval.argtypes = [C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.rt_tonemap.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
         L.rt_bvh_node_count.restype = C.c_uint32
         L.rt_bvh_node_count.argtypes = [C.c_uint32]
@@ -138,8 +148,17 @@ def _check(rc):
 
 
 def load_earth():
-    """The reference's earthmap.jpg decoded to RGB8 (committed fixture; see tests/golden/make_fixtures.py)."""
-    return np.load(os.path.join(_ROOT, "tests", "golden", "earthmap_rgb8.npz"))["rgb"]
+    """The reference's earthmap.jpg decoded to RGB8 (Scenes.hs:157-165 reads it with JuicyPixels; no JPEG decoder is assumed
+    here, so the decoded texels ship with the package: ray-tracing_b200/data/earthmap_rgb8.npz, made by tests/golden/make_fixtures.py in the build container)."""
+    return np.load(os.path.join(_HERE, "data", "earthmap_rgb8.npz"))["rgb"]
+
+
+def init_gpus(n=0, nccl=False):
+    """rt_init: make n devices (0 = all visible) the default of every later render(); returns the number in use."""
+    rc = core().rt_init(n, INIT_NCCL if nccl else 0)
+    if rc < 0:
+        _check(rc)
+    return rc
 
 
 from ._scene import HostScene, DeviceScene, desc_arrays  # noqa: E402,F401

@@ -3,7 +3,7 @@ import ctypes as C
 
 import numpy as np
 
-from . import (PREC_F32, RtRenderParams, RtSceneDesc, RtStats, COUNTER_NAMES, _check, _p, core, host, load_earth)
+from . import (PREC_DEFAULT, REDUCE_KINDS, RtRenderParams, RtSceneDesc, RtStats, COUNTER_NAMES, _check, _p, core, host, load_earth)
 
 
 def _arr(ptr, n, dtype):
@@ -103,9 +103,9 @@ class DeviceScene:
     __del__ = destroy
 
     @staticmethod
-    def params(W, H, spp, depth=50, seed=1, s0=0, region=None, precision=PREC_F32, flags=0, total=None):
+    def params(W, H, spp, depth=50, seed=1, s0=0, region=None, precision=PREC_DEFAULT, flags=0, total=None, n_gpus=0):
         r0, r1, c0, c1 = region if region else (0, 0, 0, 0)
-        return RtRenderParams(W, H, s0, spp, total or spp, depth, r0, r1, c0, c1, seed, precision, flags, -1, 0)
+        return RtRenderParams(W, H, s0, spp, total or spp, depth, r0, r1, c0, c1, seed, precision, flags, -1, n_gpus)
 
     def render(self, W, H, spp, counted=False, out=None, **kw):
         """-> (radiance sums float64 [H,W,3], stats dict)"""
@@ -114,7 +114,9 @@ class DeviceScene:
         st = RtStats()
         fn = core().rt_render_counted if counted else core().rt_render
         _check(fn(self.id, C.byref(p), _p(out), C.byref(st)))
-        stats = dict(kernel_ms=st.kernel_ms, d2h_ms=st.d2h_ms, samples=int(st.samples), launches=int(st.launches))
+        stats = dict(kernel_ms=st.kernel_ms, d2h_ms=st.d2h_ms, samples=int(st.samples), launches=int(st.launches), gpus=int(st.gpus),
+                     reduce_ms=st.reduce_ms, replicate_ms=st.replicate_ms, reduce_kind=REDUCE_KINDS[st.reduce_kind],
+                     gpu_kernel_ms=[float(x) for x in st.gpu_kernel_ms[:max(int(st.gpus), 1)]])
         if counted:
             stats["counters"] = dict(zip(COUNTER_NAMES, (int(x) for x in st.counters)))
             stats["sched"] = [int(x) for x in st.sched]
@@ -126,7 +128,17 @@ class DeviceScene:
         _check(core().rt_render_device(self.id, C.byref(p), C.c_void_p(d_ptr), C.c_void_p(stream), C.byref(st) if timed else None))
         return st.kernel_ms if timed else None
 
-    def trace(self, rays7, precision=PREC_F32, flags=0, tmin=1e-4, tmax=np.inf, seed=0, log_stride=0):
+    def render_pathlog(self, W, H, spp, max_bounces=50, **kw):
+        """-> (radiance sums, prim_log uint32 [paths, max_bounces] (0xfffffffe = bounce not reached, 0xffffffff = miss), t_log float64)"""
+        p = self.params(W, H, spp, **kw)
+        r0, r1, c0, c1 = kw.get("region") or (0, H, 0, W)
+        paths = (r1 - r0) * (c1 - c0) * spp
+        out = np.zeros((H, W, 3))
+        prim = np.full((paths, max_bounces), 0xFFFFFFFE, np.uint32); t = np.zeros((paths, max_bounces))
+        _check(core().rt_render_pathlog(self.id, C.byref(p), _p(out), max_bounces, _p(prim), _p(t)))
+        return out, prim, t
+
+    def trace(self, rays7, precision=PREC_DEFAULT, flags=0, tmin=1e-4, tmax=np.inf, seed=0, log_stride=0):
         rays7 = np.ascontiguousarray(rays7, dtype=np.float64)
         n = rays7.shape[0]
         o = dict(hit=np.zeros(n, np.int32), rec=np.zeros((n, 9)), prim=np.zeros(n, np.uint32), mat=np.zeros(n, np.uint32),
@@ -136,11 +148,20 @@ class DeviceScene:
                                _p(o["prim"]), _p(o["mat"]), _p(o["front"]), _p(o["nvisit"]), _p(o["vhash"]), _p(o["vlog"])))
         return o
 
-    def texture_value(self, tex, q5, precision=PREC_F32):
+    def texture_value(self, tex, q5, precision=PREC_DEFAULT, flags=0):
         q5 = np.ascontiguousarray(q5, dtype=np.float64)
         out = np.zeros((q5.shape[0], 3))
-        _check(core().rt_texture_value(self.id, tex, precision, q5.shape[0], _p(q5), _p(out)))
+        _check(core().rt_texture_value(self.id, tex, precision, flags, q5.shape[0], _p(q5), _p(out)))
         return out
+
+
+def strict_math_eval(fn, x, y=None, as_float=False):
+    """rt_strict_math_eval: the shared strict-math functions evaluated on the device (fn: sin cos atan2 asin log)."""
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    y = np.zeros_like(x) if y is None else np.ascontiguousarray(y, dtype=np.float64)
+    out = np.zeros_like(x)
+    _check(core().rt_strict_math_eval(["sin", "cos", "atan2", "asin", "log"].index(fn), x.size, _p(x), _p(y), _p(out), int(as_float)))
+    return out
 
 
 def tonemap(rgb_sum, total_samples):

@@ -6,10 +6,14 @@
 #include "rt_device.cuh"
 #include "rt_launch.h"
 
+#include <dlfcn.h>
+
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -45,27 +49,54 @@ struct HostScene {
 };
 
 template <class T> struct DevBuffers {
-  std::vector<void*> allocs;
+  void* blob = nullptr;  // ONE device allocation holds every array of the scene (256-byte aligned sub-ranges)
   DScene<T> sc{};
   bool ready = false;
-  ~DevBuffers() { for (void* p : allocs) cudaFree(p); }
+  ~DevBuffers() { if (blob) cudaFree(blob); }
 };
 
-struct SceneEntry {
-  std::mutex mu;  // calls on one handle are serialised: they share the device scene, the work counter and the staging buffers
-  HostScene hs;
+// everything a scene owns on ONE device: the packed scene (fp32 eagerly, fp64 on first use), the work counters, a framebuffer
+struct DeviceCtx {
   int device = 0, numSMs = 148;
   DevBuffers<float> f32;
   DevBuffers<double> f64;
   unsigned long long* d_counter = nullptr;  // [0] path counter, [1..16] work counters, [17..32] scheduler statistics
   double* d_fb = nullptr; size_t fbElems = 0;
-  double* h_fb = nullptr; size_t hfbElems = 0;  // pinned staging
-  ~SceneEntry() {
+  cudaStream_t stream = nullptr;            // multi-GPU shares only (the single-device entry points use the caller's / default stream)
+  cudaEvent_t evStart = nullptr, evDone = nullptr;
+  ~DeviceCtx() {
     if (d_counter) cudaFree(d_counter);
     if (d_fb) cudaFree(d_fb);
-    if (h_fb) cudaFreeHost(h_fb);
+    if (evStart) cudaEventDestroy(evStart);
+    if (evDone) cudaEventDestroy(evDone);
+    if (stream) cudaStreamDestroy(stream);
   }
 };
+
+struct SceneEntry {
+  std::mutex mu;  // calls on one handle are serialised: they share the device scene, the work counter and the staging buffers
+  HostScene hs;
+  DeviceCtx main;                                         // the device given to rt_scene_create
+  std::map<int, std::unique_ptr<DeviceCtx>> replicas;     // other devices, filled by multi-GPU rt_render calls
+  double* h_fb = nullptr; size_t hfbElems = 0;  // pinned staging
+  ~SceneEntry() { if (h_fb) cudaFreeHost(h_fb); }
+};
+
+// library-wide multi-GPU state (rt_init)
+struct MultiGpu {
+  std::mutex mu;
+  int defaultGpus = 1;
+  bool wantNccl = false;
+  // NCCL, loaded at run time so that the library has no link-time dependency on it
+  void* lib = nullptr;
+  std::vector<void*> comms;  // ncclComm_t per device ordinal 0..n-1
+  int (*commInitAll)(void**, int, const int*) = nullptr;
+  int (*commDestroy)(void*) = nullptr;
+  int (*reduce)(const void*, void*, size_t, int, int, int, void*, cudaStream_t) = nullptr;
+  int (*groupStart)() = nullptr;
+  int (*groupEnd)() = nullptr;
+  const char* (*errorString)(int) = nullptr;
+} g_multi;
 
 std::mutex g_mu;
 std::map<uint64_t, std::shared_ptr<SceneEntry>> g_scenes;
@@ -142,16 +173,23 @@ template <class T> T fromBits(uint32_t b);
 template <> float fromBits<float>(uint32_t b) { float f; std::memcpy(&f, &b, 4); return f; }
 template <> double fromBits<double>(uint32_t b) { uint64_t w = b; double d; std::memcpy(&d, &w, 8); return d; }
 
-template <class T, class V> int upload(DevBuffers<T>& db, const std::vector<V>& host, const V** out) {
-  *out = nullptr;
-  if (host.empty()) return RT_OK;
-  void* p = nullptr;
-  CU(cudaMalloc(&p, host.size() * sizeof(V)));
-  db.allocs.push_back(p);
-  CU(cudaMemcpy(p, host.data(), host.size() * sizeof(V), cudaMemcpyHostToDevice));
-  *out = static_cast<const V*>(p);
-  return RT_OK;
-}
+// Scene upload: every array is laid out in ONE pinned staging buffer (kept for the life of the library, grown on demand) and goes
+// to the device as ONE allocation and ONE cudaMemcpyAsync (round 1 did a cudaMalloc + a pageable cudaMemcpy per array, ~16 per scene).
+struct PinnedStage {
+  std::mutex mu; char* p = nullptr; size_t cap = 0;
+  ~PinnedStage() { if (p) cudaFreeHost(p); }
+} g_stage;
+struct BlobLayout {
+  struct Piece { size_t off; const void* src; size_t bytes; };
+  std::vector<Piece> pieces; size_t total = 0;
+  size_t add(const void* src, size_t bytes) {
+    const size_t off = total;
+    if (bytes) pieces.push_back({off, src, bytes});
+    total += (bytes + 255) & ~(size_t)255;
+    return off;
+  }
+  template <class V> size_t add(const std::vector<V>& v) { return add(v.data(), v.size() * sizeof(V)); }
+};
 
 // which leaf classes are tested as pairs (bit 0 sphere-like, bit 1 rect / cuboid): sphere pairs always pay; rect / cuboid pairs pay
 // in cuboid-heavy scenes (cfg3 +3 %) and cost in rect scenes (cfg4 -9 %).  RTB_PAIR overrides for experiments.
@@ -209,31 +247,45 @@ template <class T> int buildDevice(const HostScene& h, DevBuffers<T>& db) {
   for (size_t i = 0; i < (size_t)h.n_perlin * 768; ++i) pperm[i] = (uint8_t)(h.perlin_perm[i] & 255);
 
   DScene<T>& sc = db.sc;
-  int rc;
-  if ((rc = upload(db, nodes, &sc.nodes))) return rc;
-  if ((rc = upload(db, nsz, &sc.node_sz))) return rc;
-  if ((rc = upload(db, spheres, &sc.spheres))) return rc;
-  if ((rc = upload(db, h.sphere_mat, &sc.sphere_mat))) return rc;
-  if ((rc = upload(db, moving, &sc.moving))) return rc;
-  if ((rc = upload(db, rects, &sc.rects))) return rc;
-  if ((rc = upload(db, cuboids, &sc.cuboids))) return rc;
-  if ((rc = upload(db, translates, &sc.translates))) return rc;
-  if ((rc = upload(db, rotates, &sc.rotates))) return rc;
-  if ((rc = upload(db, media, &sc.media))) return rc;
-  if ((rc = upload(db, mats, &sc.mats))) return rc;
-  if ((rc = upload(db, texs, &sc.texs))) return rc;
-  if ((rc = upload(db, pvec, &sc.perlin_vec))) return rc;
-  if ((rc = upload(db, pperm, &sc.perlin_perm))) return rc;
+  BlobLayout L;
+  const size_t oNodes = L.add(nodes), oNsz = L.add(nsz), oSph = L.add(spheres), oSmat = L.add(h.sphere_mat), oMov = L.add(moving), oRect = L.add(rects),
+               oCub = L.add(cuboids), oTr = L.add(translates), oRot = L.add(rotates), oMed = L.add(media), oMat = L.add(mats), oTex = L.add(texs),
+               oPv = L.add(pvec), oPp = L.add(pperm);
   std::vector<DImage> imgs(h.n_images);
-  for (size_t i = 0; i < h.n_images; ++i) {
-    size_t npx = (size_t)h.image_w[i] * h.image_h[i];
-    std::vector<uchar4> px(npx);
-    for (size_t p = 0; p < npx; ++p) px[p] = make_uchar4(h.images[i][p * 3], h.images[i][p * 3 + 1], h.images[i][p * 3 + 2], 255);
-    const uchar4* dp = nullptr;
-    if ((rc = upload(db, px, &dp))) return rc;
-    imgs[i] = DImage{dp, h.image_w[i], h.image_h[i], 0};
+  std::vector<size_t> oImg(h.n_images);
+  for (size_t i = 0; i < h.n_images; ++i) oImg[i] = L.add(nullptr, (size_t)h.image_w[i] * h.image_h[i] * sizeof(uchar4));
+  const size_t oImgTab = L.add(nullptr, imgs.size() * sizeof(DImage));
+  const size_t total = std::max<size_t>(L.total, 256);
+  CU(cudaMalloc(&db.blob, total));
+  char* base = static_cast<char*>(db.blob);
+  {
+    std::lock_guard<std::mutex> lk(g_stage.mu);
+    if (g_stage.cap < total) {
+      if (g_stage.p) cudaFreeHost(g_stage.p);
+      g_stage.p = nullptr; g_stage.cap = 0;
+      CU(cudaHostAlloc(reinterpret_cast<void**>(&g_stage.p), total, cudaHostAllocDefault));
+      g_stage.cap = total;
+    }
+    for (const auto& pc : L.pieces) if (pc.src) std::memcpy(g_stage.p + pc.off, pc.src, pc.bytes);
+    for (size_t i = 0; i < h.n_images; ++i) {  // RGB8 -> uchar4 directly in the staging buffer
+      uchar4* px = reinterpret_cast<uchar4*>(g_stage.p + oImg[i]);
+      const size_t npx = (size_t)h.image_w[i] * h.image_h[i];
+      for (size_t q = 0; q < npx; ++q) px[q] = make_uchar4(h.images[i][q * 3], h.images[i][q * 3 + 1], h.images[i][q * 3 + 2], 255);
+      imgs[i] = DImage{reinterpret_cast<const uchar4*>(base + oImg[i]), h.image_w[i], h.image_h[i], 0};
+    }
+    if (!imgs.empty()) std::memcpy(g_stage.p + oImgTab, imgs.data(), imgs.size() * sizeof(DImage));
+    CU(cudaMemcpyAsync(base, g_stage.p, L.total, cudaMemcpyHostToDevice, 0));
+    CU(cudaStreamSynchronize(0));
   }
-  if ((rc = upload(db, imgs, &sc.images))) return rc;
+  auto at = [&](size_t off, size_t count) -> const void* { return count ? base + off : nullptr; };
+  sc.nodes = static_cast<const Q*>(at(oNodes, nodes.size())); sc.node_sz = static_cast<const uint4*>(at(oNsz, nsz.size()));
+  sc.spheres = static_cast<const Q*>(at(oSph, spheres.size())); sc.sphere_mat = static_cast<const uint32_t*>(at(oSmat, h.sphere_mat.size()));
+  sc.moving = static_cast<const Q*>(at(oMov, moving.size())); sc.rects = static_cast<const Q*>(at(oRect, rects.size()));
+  sc.cuboids = static_cast<const Q*>(at(oCub, cuboids.size())); sc.translates = static_cast<const Q*>(at(oTr, translates.size()));
+  sc.rotates = static_cast<const Q*>(at(oRot, rotates.size())); sc.media = static_cast<const Q*>(at(oMed, media.size()));
+  sc.mats = static_cast<const Q*>(at(oMat, mats.size())); sc.texs = static_cast<const Q*>(at(oTex, texs.size()));
+  sc.perlin_vec = static_cast<const Q*>(at(oPv, pvec.size())); sc.perlin_perm = static_cast<const uint8_t*>(at(oPp, pperm.size()));
+  sc.images = static_cast<const DImage*>(at(oImgTab, imgs.size()));
   sc.world_root = h.world_root; sc.lights_root = h.lights_root;
   sc.bigCoords = 0; sc.pad_ = 0;
   for (double v : h.node_box) if (!(std::fabs(v) <= 1099511627776.0)) sc.bigCoords = 1;  // beyond 2^40 or non-finite (rt_device.cuh kDivHi)
@@ -258,10 +310,10 @@ struct Events {
   ~Events() { for (int i = 0; i < n; ++i) cudaEventDestroy(ev[i]); }
 };
 
-int deviceScene(SceneEntry* e, uint32_t precision, const void** out) {
+int deviceScene(const HostScene& hs, DeviceCtx* c, uint32_t precision, const void** out) {
   int rc;
-  if (precision == RT_PREC_F64) { if ((rc = buildDevice<double>(e->hs, e->f64))) return rc; *out = &e->f64.sc; }
-  else if (precision == RT_PREC_F32 || precision == RT_PREC_MIXED) { if ((rc = buildDevice<float>(e->hs, e->f32))) return rc; *out = &e->f32.sc; }
+  if (precision == RT_PREC_F64) { if ((rc = buildDevice<double>(hs, c->f64))) return rc; *out = &c->f64.sc; }
+  else if (precision == RT_PREC_F32 || precision == RT_PREC_MIXED) { if ((rc = buildDevice<float>(hs, c->f32))) return rc; *out = &c->f32.sc; }
   else return fail(RT_ERR_ARG, "bad precision");
   return RT_OK;
 }
@@ -275,6 +327,7 @@ int normaliseParams(const RtRenderParams* p, RtRenderParams& q) {
   if (q.col0 == 0 && q.col1 == 0) q.col1 = q.width;
   if (q.row1 > q.height || q.col1 > q.width || q.row0 >= q.row1 || q.col0 >= q.col1) return fail(RT_ERR_ARG, "bad region");
   if (q.precision > RT_PREC_F64) return fail(RT_ERR_ARG, "bad precision");
+  if ((q.flags & RT_FLAG_FAST_MATH) && (q.flags & RT_FLAG_STRICT_MATH)) return fail(RT_ERR_ARG, "RT_FLAG_FAST_MATH and RT_FLAG_STRICT_MATH exclude each other");
   return RT_OK;
 }
 
@@ -284,13 +337,15 @@ uint32_t tuneParam(const char* name, uint32_t dflt) {
   return v ? (uint32_t)std::strtoul(v, nullptr, 10) : dflt;
 }
 
-// launches the render kernel into d_out (accumulating); counters optional
-int renderLaunch(SceneEntry* e, const RtRenderParams& q, double* d_out, cudaStream_t st, bool counted, int* gridOut) {
+struct PathLog { uint32_t* prim = nullptr; double* t = nullptr; uint32_t stride = 0; };
+
+// launches the render kernel of one device into d_out (accumulating).  instr: 0 production, 1 counters, 3 path log
+int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, double* d_out, cudaStream_t st, int instr, int* gridOut, const PathLog* plog = nullptr) {
   const void* dsc = nullptr;
-  int rc = deviceScene(e, q.precision, &dsc);
+  int rc = deviceScene(hs, c, q.precision, &dsc);
   if (rc) return rc;
-  if (!e->d_counter) { CU(cudaMalloc(&e->d_counter, 33 * sizeof(unsigned long long))); }
-  CU(cudaMemsetAsync(e->d_counter, 0, 33 * sizeof(unsigned long long), st));
+  if (!c->d_counter) { CU(cudaMalloc(&c->d_counter, 33 * sizeof(unsigned long long))); }
+  CU(cudaMemsetAsync(c->d_counter, 0, 33 * sizeof(unsigned long long), st));
   if (q.sample_count == 0) return RT_OK;
   RenderArgs a{};
   a.W = q.width; a.H = q.height; a.s0 = q.sample_offset; a.ns = q.sample_count; a.maxDepth = q.max_depth;
@@ -300,7 +355,7 @@ int renderLaunch(SceneEntry* e, const RtRenderParams& q, double* d_out, cudaStre
   // chunk: ~1024 paths, halved until there are at least 8 chunks per warp slot for balance, down to 4 paths: launches with few, very
   // long paths (the cfg5 sample: seconds per path) are tail-bound, and a warp that refills 4 lanes at a time keeps its lanes busier than
   // one that waits for a 32-path chunk to drain (tools/chunk_probe.py: 90 k spheres, 480x270x1: 1424 -> 1242 ms; results are identical)
-  unsigned long long warps = (unsigned long long)e->numSMs * 16ull;
+  unsigned long long warps = (unsigned long long)c->numSMs * 16ull;
   unsigned long long chunk = 1024;
   const unsigned long long chunkMin = std::max(1u, tuneParam("RTB_CHUNK_MIN", 4));
   while (chunk > chunkMin && a.total_paths / chunk < warps * 8ull) chunk /= 2;
@@ -308,20 +363,193 @@ int renderLaunch(SceneEntry* e, const RtRenderParams& q, double* d_out, cudaStre
   // scheduler thresholds (rt_render_kernel.inl): single rects are cheap steps and worth running for 3 lanes, cuboid-heavy scenes batch
   // 6; media make the rare class frequent (3 rare steps per medium visit) and worth running for 4 lanes.  Measured on the
   // reference scenes (tools/knob_sweep.py); results never depend on these.
-  const HostScene& hs = e->hs;
   a.shadeMin = tuneParam("RTB_SHADE_MIN", 16);
   a.rectMin = std::max(1u, tuneParam("RTB_RECT_MIN", hs.n_cuboids > hs.n_rects ? 6u : 3u));
   a.rareMin = std::max(1u, tuneParam("RTB_RARE_MIN", hs.n_media > 0 ? 4u : 8u));
   a.keepNode = std::max(1u, tuneParam("RTB_KEEP_NODE", 12)); a.keepLeaf = std::max(1u, tuneParam("RTB_KEEP_LEAF", 8));
   a.lightCap = hs.lightCap;
-  a.counter = e->d_counter; a.ctr = counted ? e->d_counter + 1 : nullptr; a.out = d_out;
-  cudaError_t ce = (q.flags & RT_FLAG_FAST_MATH) ? launchRender<true>((int)q.precision, counted ? 1 : 0, dsc, a, e->hs.stackDepth, e->numSMs, st, gridOut)
-                                                 : launchRender<false>((int)q.precision, counted ? 1 : 0, dsc, a, e->hs.stackDepth, e->numSMs, st, gridOut);
+  a.counter = c->d_counter; a.ctr = instr == 1 ? c->d_counter + 1 : nullptr; a.out = d_out;
+  if (plog) { a.plogPrim = plog->prim; a.plogT = plog->t; a.plogStride = plog->stride; }
+  cudaError_t ce;
+  if (q.flags & RT_FLAG_FAST_MATH) ce = launchRender<MATH_FAST>((int)q.precision, instr == 3 ? 0 : instr, dsc, a, hs.stackDepth, c->numSMs, st, gridOut);
+  else if (q.flags & RT_FLAG_STRICT_MATH) ce = launchRender<MATH_STRICT>((int)q.precision, instr, dsc, a, hs.stackDepth, c->numSMs, st, gridOut);
+  else ce = launchRender<MATH_LITERAL>((int)q.precision, instr, dsc, a, hs.stackDepth, c->numSMs, st, gridOut);
   if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("render launch: ") + cudaGetErrorString(ce));
   return RT_OK;
 }
 
-int renderHost(rt_scene_t scene, const RtRenderParams* params, double* out, RtStats* stats, bool counted) {
+int ensureFramebuffer(DeviceCtx* c, size_t elems) {
+  if (c->fbElems < elems) {
+    if (c->d_fb) cudaFree(c->d_fb);
+    c->d_fb = nullptr; c->fbElems = 0;
+    CU(cudaMalloc(&c->d_fb, elems * sizeof(double)));
+    c->fbElems = elems;
+  }
+  return RT_OK;
+}
+int ensureHostStaging(SceneEntry* e, size_t elems) {
+  if (e->hfbElems < elems) {
+    if (e->h_fb) cudaFreeHost(e->h_fb);
+    e->h_fb = nullptr; e->hfbElems = 0;
+    CU(cudaHostAlloc(&e->h_fb, elems * sizeof(double), cudaHostAllocDefault));
+    e->hfbElems = elems;
+  }
+  return RT_OK;
+}
+
+// ---- multi-GPU inside rt_render: the frame's samples are split into contiguous slices over the devices (row bands
+// when there are fewer samples than devices), every device renders its share into its own double framebuffer on its own stream, and
+// the partial sums are added onto the scene's device: by ONE kernel there that reads the peers' buffers over NVLink (peer access),
+// or by ncclReduce when rt_init asked for NCCL, or through staged peer copies when the devices cannot address each other.
+int ensureReplica(SceneEntry* e, int device, DeviceCtx** out) {
+  if (device == e->main.device) { *out = &e->main; }
+  else {
+    auto& slot = e->replicas[device];
+    if (!slot) {
+      slot.reset(new DeviceCtx());
+      slot->device = device;
+      cudaDeviceProp prop;
+      CU(cudaGetDeviceProperties(&prop, device));
+      slot->numSMs = prop.multiProcessorCount;
+    }
+    *out = slot.get();
+  }
+  DeviceCtx* c = *out;
+  CU(cudaSetDevice(device));
+  if (!c->stream) {
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&c->evStart)); CU(cudaEventCreate(&c->evDone));
+  }
+  return RT_OK;
+}
+
+int renderMulti(SceneEntry* e, const RtRenderParams& q, int nGpus, double* out, RtStats* stats) {
+  const size_t elems = (size_t)q.width * q.height * 3;
+  std::vector<int> devs{e->main.device};
+  for (int d = 0; d < nGpus && (int)devs.size() < nGpus; ++d) if (d != e->main.device) devs.push_back(d);
+  const int n = (int)devs.size();
+  std::vector<DeviceCtx*> ctx(n);
+  const auto t0 = std::chrono::steady_clock::now();
+  bool replicated = false;
+  for (int k = 0; k < n; ++k) {
+    int rc = ensureReplica(e, devs[k], &ctx[k]);
+    if (rc) return rc;
+    const bool had = (q.precision == RT_PREC_F64) ? ctx[k]->f64.ready : ctx[k]->f32.ready;
+    const void* dsc = nullptr;
+    if ((rc = deviceScene(e->hs, ctx[k], q.precision, &dsc))) return rc;  // replication happens here, once per device and layout
+    replicated = replicated || !had;
+    if ((rc = ensureFramebuffer(ctx[k], elems))) return rc;
+  }
+  const double replicateMs = replicated ? std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count() : 0.0;
+  int rc = ensureHostStaging(e, elems);
+  if (rc) return rc;
+  // peer access root <- k
+  DeviceCtx* root = ctx[0];
+  bool allPeer = true;
+  CU(cudaSetDevice(root->device));
+  for (int k = 1; k < n; ++k) {
+    int can = 0;
+    CU(cudaDeviceCanAccessPeer(&can, root->device, devs[k]));
+    if (can) {
+      cudaError_t pe = cudaDeviceEnablePeerAccess(devs[k], 0);
+      if (pe == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+      else if (pe != cudaSuccess) { cudaGetLastError(); can = 0; }
+    }
+    allPeer = allPeer && can;
+  }
+  // shares
+  const bool bySamples = q.sample_count >= (uint32_t)n;
+  const uint32_t rows = q.row1 - q.row0;
+  for (int k = 0; k < n; ++k) {
+    RtRenderParams qk = q;
+    if (bySamples) {
+      const uint32_t base = q.sample_count / n, rem = q.sample_count % n;
+      qk.sample_offset = q.sample_offset + k * base + std::min<uint32_t>(k, rem);
+      qk.sample_count = base + ((uint32_t)k < rem ? 1u : 0u);
+    } else {
+      const uint32_t base = rows / n, rem = rows % n;
+      qk.row0 = q.row0 + k * base + std::min<uint32_t>(k, rem);
+      qk.row1 = qk.row0 + base + ((uint32_t)k < rem ? 1u : 0u);
+      if (qk.row1 <= qk.row0) qk.sample_count = 0;
+    }
+    CU(cudaSetDevice(devs[k]));
+    CU(cudaMemsetAsync(ctx[k]->d_fb, 0, elems * sizeof(double), ctx[k]->stream));
+    CU(cudaEventRecord(ctx[k]->evStart, ctx[k]->stream));
+    if ((rc = renderLaunch(e->hs, ctx[k], qk, ctx[k]->d_fb, ctx[k]->stream, 0, nullptr))) return rc;
+    CU(cudaEventRecord(ctx[k]->evDone, ctx[k]->stream));
+  }
+  // reduction onto the root
+  CU(cudaSetDevice(root->device));
+  Events evs;
+  CU(evs.create(3));
+  uint32_t kind = RT_REDUCE_NONE;
+  bool useNccl = false;
+  {
+    std::lock_guard<std::mutex> lk(g_multi.mu);
+    useNccl = g_multi.wantNccl && !g_multi.comms.empty();
+    for (int k = 0; k < n && useNccl; ++k) if (devs[k] >= (int)g_multi.comms.size()) useNccl = false;
+    if (useNccl && (int)g_multi.comms.size() != n) useNccl = false;  // the communicator spans exactly the rt_init devices
+  }
+  if (n > 1 && useNccl) {
+    kind = RT_REDUCE_NCCL;
+    CU(cudaEventRecord(evs.ev[0], root->stream));
+    int nrc = g_multi.groupStart();
+    for (int k = 0; k < n && nrc == 0; ++k)
+      nrc = g_multi.reduce(ctx[k]->d_fb, ctx[k]->d_fb, elems, /*ncclFloat64*/ 8, /*ncclSum*/ 0, root->device, g_multi.comms[devs[k]], ctx[k]->stream);
+    const int grc = g_multi.groupEnd();
+    if (nrc == 0) nrc = grc;
+    if (nrc != 0) return fail(RT_ERR_CUDA, std::string("ncclReduce: ") + (g_multi.errorString ? g_multi.errorString(nrc) : "error"));
+    CU(cudaEventRecord(evs.ev[1], root->stream));
+  } else {
+    for (int k = 1; k < n; ++k) CU(cudaStreamWaitEvent(root->stream, ctx[k]->evDone, 0));
+    CU(cudaEventRecord(evs.ev[0], root->stream));
+    if (n > 1 && allPeer) {
+      kind = RT_REDUCE_PEER;
+      const double* src[16] = {nullptr};
+      for (int k = 1; k < n; ++k) src[k - 1] = ctx[k]->d_fb;
+      cudaError_t ce = launchReducePeer(root->d_fb, src, n - 1, elems, root->numSMs, root->stream);
+      if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("reduce launch: ") + cudaGetErrorString(ce));
+    } else if (n > 1) {
+      kind = RT_REDUCE_STAGED;
+      double* tmp = nullptr;
+      CU(cudaMalloc(&tmp, elems * sizeof(double)));
+      for (int k = 1; k < n; ++k) {
+        CU(cudaMemcpyPeerAsync(tmp, root->device, ctx[k]->d_fb, devs[k], elems * sizeof(double), root->stream));
+        const double* src[16] = {tmp};
+        cudaError_t ce = launchReducePeer(root->d_fb, src, 1, elems, root->numSMs, root->stream);
+        if (ce != cudaSuccess) { cudaFree(tmp); return fail(RT_ERR_CUDA, std::string("reduce launch: ") + cudaGetErrorString(ce)); }
+      }
+      CU(cudaStreamSynchronize(root->stream));
+      cudaFree(tmp);
+    }
+    CU(cudaEventRecord(evs.ev[1], root->stream));
+  }
+  const size_t rowElems = (size_t)q.width * 3;
+  CU(cudaMemcpyAsync(e->h_fb + q.row0 * rowElems, root->d_fb + q.row0 * rowElems, (size_t)(q.row1 - q.row0) * rowElems * sizeof(double), cudaMemcpyDeviceToHost, root->stream));
+  CU(cudaEventRecord(evs.ev[2], root->stream));
+  CU(cudaEventSynchronize(evs.ev[2]));
+  for (int k = 1; k < n; ++k) { CU(cudaSetDevice(devs[k])); CU(cudaStreamSynchronize(ctx[k]->stream)); }
+  CU(cudaSetDevice(root->device));
+  for (uint32_t r = q.row0; r < q.row1; ++r)
+    std::memcpy(out + r * rowElems + (size_t)q.col0 * 3, e->h_fb + r * rowElems + (size_t)q.col0 * 3, (size_t)(q.col1 - q.col0) * 3 * sizeof(double));
+  if (stats) {
+    std::memset(stats, 0, sizeof(*stats));
+    float ms = 0;
+    for (int k = 0; k < n; ++k) {
+      cudaEventElapsedTime(&ms, ctx[k]->evStart, ctx[k]->evDone);
+      if (k < 16) stats->gpu_kernel_ms[k] = ms;
+      stats->kernel_ms = std::max(stats->kernel_ms, (double)ms);
+    }
+    cudaEventElapsedTime(&ms, evs.ev[0], evs.ev[1]); stats->reduce_ms = ms;
+    cudaEventElapsedTime(&ms, evs.ev[1], evs.ev[2]); stats->d2h_ms = ms;
+    stats->samples = (uint64_t)(q.row1 - q.row0) * (q.col1 - q.col0) * q.sample_count;
+    stats->launches = (uint64_t)n + (kind == RT_REDUCE_PEER ? 1 : 0);
+    stats->gpus = (uint32_t)n; stats->reduce_kind = kind; stats->replicate_ms = replicateMs;
+  }
+  return RT_OK;
+}
+
+int renderHost(rt_scene_t scene, const RtRenderParams* params, double* out, RtStats* stats, int instr, const PathLog* hostLog = nullptr) {
   const std::shared_ptr<SceneEntry> ep = lookup(scene);
   if (!ep) return fail(RT_ERR_HANDLE, "unknown scene handle");
   SceneEntry* e = ep.get();
@@ -330,47 +558,61 @@ int renderHost(rt_scene_t scene, const RtRenderParams* params, double* out, RtSt
   RtRenderParams q;
   int rc = normaliseParams(params, q);
   if (rc) return rc;
-  CU(cudaSetDevice(e->device));
+  int nGpus = (int)q.n_gpus;
+  if (nGpus == 0) { std::lock_guard<std::mutex> lk2(g_multi.mu); nGpus = g_multi.defaultGpus; }
+  if (nGpus > 1 && instr == 0) {
+    int ndev = 0;
+    CU(cudaGetDeviceCount(&ndev));
+    if (nGpus > ndev) return fail(RT_ERR_ARG, "n_gpus exceeds the number of visible devices");
+    if (nGpus > 16) return fail(RT_ERR_ARG, "n_gpus > 16");
+    return renderMulti(e, q, nGpus, out, stats);
+  }
+  DeviceCtx* c = &e->main;
+  CU(cudaSetDevice(c->device));
   const size_t elems = (size_t)q.width * q.height * 3;
-  if (e->fbElems < elems) {
-    if (e->d_fb) cudaFree(e->d_fb);
-    e->d_fb = nullptr; e->fbElems = 0;
-    CU(cudaMalloc(&e->d_fb, elems * sizeof(double)));
-    e->fbElems = elems;
-  }
-  if (e->hfbElems < elems) {
-    if (e->h_fb) cudaFreeHost(e->h_fb);
-    e->h_fb = nullptr; e->hfbElems = 0;
-    CU(cudaHostAlloc(&e->h_fb, elems * sizeof(double), cudaHostAllocDefault));
-    e->hfbElems = elems;
-  }
+  if ((rc = ensureFramebuffer(c, elems))) return rc;
+  if ((rc = ensureHostStaging(e, elems))) return rc;
   Events evs;
   CU(evs.create(3));
   const cudaEvent_t e0 = evs.ev[0], e1 = evs.ev[1], e2 = evs.ev[2];
-  CU(cudaMemsetAsync(e->d_fb, 0, elems * sizeof(double), 0));
+  struct Buf { void* p = nullptr; ~Buf() { if (p) cudaFree(p); } } dPrim, dT;
+  PathLog dlog;
+  const size_t paths = (size_t)(q.row1 - q.row0) * (q.col1 - q.col0) * q.sample_count;
+  if (instr == 3) {
+    const size_t cells = paths * hostLog->stride;
+    CU(cudaMalloc(&dPrim.p, std::max<size_t>(cells, 1) * 4)); CU(cudaMalloc(&dT.p, std::max<size_t>(cells, 1) * 8));
+    CU(cudaMemcpy(dPrim.p, hostLog->prim, cells * 4, cudaMemcpyHostToDevice)); CU(cudaMemcpy(dT.p, hostLog->t, cells * 8, cudaMemcpyHostToDevice));
+    dlog.prim = (uint32_t*)dPrim.p; dlog.t = (double*)dT.p; dlog.stride = hostLog->stride;
+  }
+  CU(cudaMemsetAsync(c->d_fb, 0, elems * sizeof(double), 0));
   CU(cudaEventRecord(e0, 0));
   int grid = 0;
-  rc = renderLaunch(e, q, e->d_fb, 0, counted, &grid);
+  rc = renderLaunch(e->hs, c, q, c->d_fb, 0, instr, &grid, instr == 3 ? &dlog : nullptr);
   if (rc) return rc;
   CU(cudaEventRecord(e1, 0));
   // copy back only the rows of the region
   const size_t rowElems = (size_t)q.width * 3;
-  CU(cudaMemcpyAsync(e->h_fb + q.row0 * rowElems, e->d_fb + q.row0 * rowElems, (size_t)(q.row1 - q.row0) * rowElems * sizeof(double), cudaMemcpyDeviceToHost, 0));
+  CU(cudaMemcpyAsync(e->h_fb + q.row0 * rowElems, c->d_fb + q.row0 * rowElems, (size_t)(q.row1 - q.row0) * rowElems * sizeof(double), cudaMemcpyDeviceToHost, 0));
   CU(cudaEventRecord(e2, 0));
   CU(cudaEventSynchronize(e2));
   for (uint32_t r = q.row0; r < q.row1; ++r)
     std::memcpy(out + r * rowElems + (size_t)q.col0 * 3, e->h_fb + r * rowElems + (size_t)q.col0 * 3, (size_t)(q.col1 - q.col0) * 3 * sizeof(double));
+  if (instr == 3) {
+    const size_t cells = paths * hostLog->stride;
+    CU(cudaMemcpy(hostLog->prim, dPrim.p, cells * 4, cudaMemcpyDeviceToHost)); CU(cudaMemcpy(hostLog->t, dT.p, cells * 8, cudaMemcpyDeviceToHost));
+  }
   if (stats) {
     std::memset(stats, 0, sizeof(*stats));
     float ms = 0;
-    cudaEventElapsedTime(&ms, e0, e1); stats->kernel_ms = ms;
+    cudaEventElapsedTime(&ms, e0, e1); stats->kernel_ms = ms; stats->gpu_kernel_ms[0] = ms;
     cudaEventElapsedTime(&ms, e1, e2); stats->d2h_ms = ms;
-    stats->samples = (uint64_t)(q.row1 - q.row0) * (q.col1 - q.col0) * q.sample_count;
+    stats->samples = (uint64_t)paths;
     stats->launches = q.sample_count ? 1 : 0;
-    if (counted) {
-      unsigned long long c[33];
-      CU(cudaMemcpy(c, e->d_counter, sizeof(c), cudaMemcpyDeviceToHost));
-      for (int i = 0; i < 16; ++i) { stats->counters[i] = c[i + 1]; stats->sched[i] = c[i + 17]; }
+    stats->gpus = 1;
+    if (instr == 1) {
+      unsigned long long cc[33];
+      CU(cudaMemcpy(cc, c->d_counter, sizeof(cc), cudaMemcpyDeviceToHost));
+      for (int i = 0; i < 16; ++i) { stats->counters[i] = cc[i + 1]; stats->sched[i] = cc[i + 17]; }
     }
   }
   return RT_OK;
@@ -392,7 +634,52 @@ int rt_device_count(void) {
 int rt_get_limits(RtLimits* out) {
   if (!out) return fail(RT_ERR_ARG, "out is null");
   out->max_stack = kMaxStack; out->max_frames = kMaxFrames; out->max_medium_depth = 1; out->max_light_depth = kMaxLightDepth;
+  out->max_tex_depth = kMaxTexDepth;
   return RT_OK;
+}
+
+int rt_init(int n_gpus, uint32_t flags) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(RT_ERR_CUDA, "no CUDA device available (this library has no CPU path)"); }
+  if (n_gpus < 0 || n_gpus > ndev) return fail(RT_ERR_ARG, "n_gpus out of range");
+  if (n_gpus == 0) n_gpus = ndev;
+  if (n_gpus > 16) return fail(RT_ERR_ARG, "n_gpus > 16");
+  std::lock_guard<std::mutex> lk(g_multi.mu);
+  // peer access between every pair (the reduction reads the peers' framebuffers from whichever device owns the scene)
+  for (int a = 0; a < n_gpus; ++a) {
+    CU(cudaSetDevice(a));
+    for (int b = 0; b < n_gpus; ++b) {
+      if (a == b) continue;
+      int can = 0;
+      if (cudaDeviceCanAccessPeer(&can, a, b) == cudaSuccess && can) { if (cudaDeviceEnablePeerAccess(b, 0) != cudaSuccess) cudaGetLastError(); }
+    }
+  }
+  CU(cudaSetDevice(0));
+  for (void* c : g_multi.comms) if (c && g_multi.commDestroy) g_multi.commDestroy(c);
+  g_multi.comms.clear();
+  g_multi.wantNccl = false;
+  if ((flags & RT_INIT_NCCL) && n_gpus > 1) {
+    if (!g_multi.lib) {
+      g_multi.lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+      if (!g_multi.lib) return fail(RT_ERR_CUDA, std::string("RT_INIT_NCCL: cannot load libnccl.so.2: ") + dlerror());
+      g_multi.commInitAll = reinterpret_cast<int (*)(void**, int, const int*)>(dlsym(g_multi.lib, "ncclCommInitAll"));
+      g_multi.commDestroy = reinterpret_cast<int (*)(void*)>(dlsym(g_multi.lib, "ncclCommDestroy"));
+      g_multi.reduce = reinterpret_cast<int (*)(const void*, void*, size_t, int, int, int, void*, cudaStream_t)>(dlsym(g_multi.lib, "ncclReduce"));
+      g_multi.groupStart = reinterpret_cast<int (*)()>(dlsym(g_multi.lib, "ncclGroupStart"));
+      g_multi.groupEnd = reinterpret_cast<int (*)()>(dlsym(g_multi.lib, "ncclGroupEnd"));
+      g_multi.errorString = reinterpret_cast<const char* (*)(int)>(dlsym(g_multi.lib, "ncclGetErrorString"));
+      if (!g_multi.commInitAll || !g_multi.commDestroy || !g_multi.reduce || !g_multi.groupStart || !g_multi.groupEnd)
+        return fail(RT_ERR_CUDA, "RT_INIT_NCCL: libnccl.so.2 lacks a required entry point");
+    }
+    std::vector<int> devs(n_gpus);
+    for (int i = 0; i < n_gpus; ++i) devs[i] = i;
+    g_multi.comms.assign(n_gpus, nullptr);
+    const int nrc = g_multi.commInitAll(g_multi.comms.data(), n_gpus, devs.data());
+    if (nrc != 0) { g_multi.comms.clear(); return fail(RT_ERR_CUDA, std::string("ncclCommInitAll: ") + (g_multi.errorString ? g_multi.errorString(nrc) : "error")); }
+    g_multi.wantNccl = true;
+  }
+  g_multi.defaultGpus = n_gpus;
+  return n_gpus;
 }
 
 int rt_scene_create(const RtSceneDesc* d, int device, rt_scene_t* out) {
@@ -460,6 +747,22 @@ int rt_scene_create(const RtSceneDesc* d, int device, rt_scene_t* out) {
     if (k == TX_PERLIN && h.tex_a[i] >= h.n_perlin) return fail(RT_ERR_ARG, "perlin table out of range");
     if (k == TX_IMAGE && h.tex_a[i] != RT_NONE && h.tex_a[i] >= h.n_images) return fail(RT_ERR_ARG, "image out of range");
   }
+  {  // checker nesting: textureValue walks at most kMaxTexDepth levels; a cycle would never end in the reference either
+    std::vector<int> depth(h.n_textures, 0);  // 0 unknown, -1 in progress, > 0 levels below and including this texture
+    bool cyc = false;
+    std::function<int(uint32_t)> levels = [&](uint32_t t) -> int {
+      if (depth[t] > 0) return depth[t];
+      if (depth[t] < 0) { cyc = true; return 1; }
+      if (h.tex_kind[t] != TX_CHECKER) return depth[t] = 1;
+      depth[t] = -1;
+      const int d = 1 + std::max(levels(h.tex_a[t]), levels(h.tex_b[t]));
+      return depth[t] = d;
+    };
+    int deepest = 0;
+    for (uint32_t i = 0; i < h.n_textures && !cyc; ++i) deepest = std::max(deepest, levels(i));
+    if (cyc) return fail(RT_ERR_ARG, "checker textures form a cycle");
+    if (deepest > kMaxTexDepth) return fail(RT_ERR_UNSUPPORTED, "more than " + std::to_string(kMaxTexDepth) + " nested CheckerTexture levels");
+  }
   if (!refOk(h, h.world_root) || !refOk(h, h.lights_root)) return fail(RT_ERR_ARG, "root ref out of range");
   Analysis an(h);
   an.go(h.world_root); an.go(h.lights_root);
@@ -484,11 +787,11 @@ int rt_scene_create(const RtSceneDesc* d, int device, rt_scene_t* out) {
   if (device < 0) { CU(cudaGetDevice(&device)); }
   if (device >= ndev) return fail(RT_ERR_ARG, "device ordinal out of range");
   CU(cudaSetDevice(device));
-  e->device = device;
+  e->main.device = device;
   cudaDeviceProp prop;
   CU(cudaGetDeviceProperties(&prop, device));
-  e->numSMs = prop.multiProcessorCount;
-  int rc = buildDevice<float>(h, e->f32);  // the production layout is uploaded eagerly; fp64 on first use
+  e->main.numSMs = prop.multiProcessorCount;
+  int rc = buildDevice<float>(h, e->main.f32);  // the production layout is uploaded eagerly; fp64 on first use
   if (rc) return rc;
   std::lock_guard<std::mutex> lk(g_mu);
   *out = g_nextId++;
@@ -507,15 +810,22 @@ int rt_scene_destroy(rt_scene_t scene) {
   }
   {
     std::lock_guard<std::mutex> lk(e->mu);  // a call in flight on another thread finishes first
-    cudaSetDevice(e->device);
+    for (auto& kv : e->replicas) { cudaSetDevice(kv.first); cudaDeviceSynchronize(); }
+    cudaSetDevice(e->main.device);
     cudaDeviceSynchronize();                // and so does asynchronous work of rt_render_device
   }
   e.reset();  // the buffers go with the last holder
   return RT_OK;
 }
 
-int rt_render(rt_scene_t scene, const RtRenderParams* params, double* out, RtStats* stats) { return renderHost(scene, params, out, stats, false); }
-int rt_render_counted(rt_scene_t scene, const RtRenderParams* params, double* out, RtStats* stats) { return renderHost(scene, params, out, stats, true); }
+int rt_render(rt_scene_t scene, const RtRenderParams* params, double* out, RtStats* stats) { return renderHost(scene, params, out, stats, 0); }
+int rt_render_counted(rt_scene_t scene, const RtRenderParams* params, double* out, RtStats* stats) { return renderHost(scene, params, out, stats, 1); }
+int rt_render_pathlog(rt_scene_t scene, const RtRenderParams* params, double* out, uint32_t max_bounces, uint32_t* prim_log, double* t_log) {
+  if (!prim_log || !t_log || max_bounces == 0) return fail(RT_ERR_ARG, "path log buffers are null / empty");
+  if (params && (params->flags & RT_FLAG_FAST_MATH)) return fail(RT_ERR_ARG, "the path log is not built for RT_FLAG_FAST_MATH");
+  PathLog log; log.prim = prim_log; log.t = t_log; log.stride = max_bounces;
+  return renderHost(scene, params, out, nullptr, 3, &log);
+}
 
 int rt_render_device(rt_scene_t scene, const RtRenderParams* params, double* d_out, void* cuda_stream, RtStats* stats) {
   const std::shared_ptr<SceneEntry> ep = lookup(scene);
@@ -526,12 +836,12 @@ int rt_render_device(rt_scene_t scene, const RtRenderParams* params, double* d_o
   RtRenderParams q;
   int rc = normaliseParams(params, q);
   if (rc) return rc;
-  CU(cudaSetDevice(e->device));
+  CU(cudaSetDevice(e->main.device));
   cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
   Events evs;
   if (stats) { CU(evs.create(2)); CU(cudaEventRecord(evs.ev[0], st)); }
   const cudaEvent_t e0 = evs.ev[0], e1 = evs.ev[1];
-  rc = renderLaunch(e, q, d_out, st, false, nullptr);
+  rc = renderLaunch(e->hs, &e->main, q, d_out, st, 0, nullptr);
   if (rc) return rc;
   if (stats) {
     CU(cudaEventRecord(e1, st));
@@ -539,6 +849,7 @@ int rt_render_device(rt_scene_t scene, const RtRenderParams* params, double* d_o
     std::memset(stats, 0, sizeof(*stats));
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
     stats->kernel_ms = ms; stats->samples = (uint64_t)(q.row1 - q.row0) * (q.col1 - q.col0) * q.sample_count; stats->launches = q.sample_count ? 1 : 0;
+    stats->gpus = 1; stats->gpu_kernel_ms[0] = ms;
   }
   return RT_OK;
 }
@@ -551,9 +862,10 @@ int rt_trace(rt_scene_t scene, uint32_t precision, uint32_t flags, uint32_t n, c
   std::lock_guard<std::mutex> lk(e->mu);
   if (!rays && n) return fail(RT_ERR_ARG, "rays is null");
   if (n == 0) return RT_OK;
-  CU(cudaSetDevice(e->device));
+  if ((flags & RT_FLAG_FAST_MATH) && (flags & RT_FLAG_STRICT_MATH)) return fail(RT_ERR_ARG, "RT_FLAG_FAST_MATH and RT_FLAG_STRICT_MATH exclude each other");
+  CU(cudaSetDevice(e->main.device));
   const void* dsc = nullptr;
-  int rc = deviceScene(e, precision, &dsc);
+  int rc = deviceScene(e->hs, &e->main, precision, &dsc);
   if (rc) return rc;
   const uint32_t stride = log_stride ? log_stride : 1;
   struct Buf { void* p = nullptr; ~Buf() { if (p) cudaFree(p); } };
@@ -567,7 +879,9 @@ int rt_trace(rt_scene_t scene, uint32_t precision, uint32_t flags, uint32_t n, c
   a.n = n; a.logStride = log_stride; a.tmin = t_min; a.tmax = t_max; a.seed = seed; a.rays = (const double*)bRays.p;
   a.hit = (int32_t*)bHit.p; a.rec = (double*)bRec.p; a.prim = (uint32_t*)bPrim.p; a.mat = (uint32_t*)bMat.p; a.front = (uint8_t*)bFront.p;
   a.nvisit = (unsigned long long*)bNv.p; a.vhash = (unsigned long long*)bVh.p; a.vlog = (uint32_t*)bLog.p;
-  cudaError_t ce = (flags & RT_FLAG_FAST_MATH) ? launchTrace<true>((int)precision, dsc, a, e->hs.stackDepth, 0) : launchTrace<false>((int)precision, dsc, a, e->hs.stackDepth, 0);
+  cudaError_t ce = (flags & RT_FLAG_FAST_MATH) ? launchTrace<MATH_FAST>((int)precision, dsc, a, e->hs.stackDepth, 0)
+                   : (flags & RT_FLAG_STRICT_MATH) ? launchTrace<MATH_STRICT>((int)precision, dsc, a, e->hs.stackDepth, 0)
+                                                   : launchTrace<MATH_LITERAL>((int)precision, dsc, a, e->hs.stackDepth, 0);
   if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("trace launch: ") + cudaGetErrorString(ce));
   CU(cudaDeviceSynchronize());
   if (hit) CU(cudaMemcpy(hit, bHit.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
@@ -581,7 +895,7 @@ int rt_trace(rt_scene_t scene, uint32_t precision, uint32_t flags, uint32_t n, c
   return RT_OK;
 }
 
-int rt_texture_value(rt_scene_t scene, uint32_t tex, uint32_t precision, uint32_t n, const double* q, double* out) {
+int rt_texture_value(rt_scene_t scene, uint32_t tex, uint32_t precision, uint32_t flags, uint32_t n, const double* q, double* out) {
   const std::shared_ptr<SceneEntry> ep = lookup(scene);
   if (!ep) return fail(RT_ERR_HANDLE, "unknown scene handle");
   SceneEntry* e = ep.get();
@@ -589,14 +903,14 @@ int rt_texture_value(rt_scene_t scene, uint32_t tex, uint32_t precision, uint32_
   if (tex >= e->hs.n_textures) return fail(RT_ERR_ARG, "texture index out of range");
   if (n == 0) return RT_OK;
   if (!q || !out) return fail(RT_ERR_ARG, "q/out is null");
-  CU(cudaSetDevice(e->device));
+  CU(cudaSetDevice(e->main.device));
   const void* dsc = nullptr;
-  int rc = deviceScene(e, precision, &dsc);
+  int rc = deviceScene(e->hs, &e->main, precision, &dsc);
   if (rc) return rc;
   double *dq = nullptr, *dout = nullptr;
   CU(cudaMalloc(&dq, (size_t)n * 5 * sizeof(double))); CU(cudaMalloc(&dout, (size_t)n * 3 * sizeof(double)));
   CU(cudaMemcpy(dq, q, (size_t)n * 5 * sizeof(double), cudaMemcpyHostToDevice));
-  cudaError_t ce = launchTexture((int)precision, dsc, tex, n, dq, dout, 0);
+  cudaError_t ce = (flags & RT_FLAG_STRICT_MATH) ? launchTexture<MATH_STRICT>((int)precision, dsc, tex, n, dq, dout, 0) : launchTexture<MATH_LITERAL>((int)precision, dsc, tex, n, dq, dout, 0);
   if (ce == cudaSuccess) ce = cudaMemcpy(out, dout, (size_t)n * 3 * sizeof(double), cudaMemcpyDeviceToHost);
   cudaFree(dq); cudaFree(dout);
   if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("texture probe: ") + cudaGetErrorString(ce));
@@ -634,9 +948,28 @@ int rt_selftest_division(uint64_t n, uint64_t seed, uint64_t* checked, uint64_t*
   return RT_OK;
 }
 
+int rt_strict_math_eval(uint32_t fn, uint32_t n, const double* x, const double* y, double* out, int as_float) {
+  if (n == 0) return RT_OK;
+  if (!x || !y || !out || fn > 4) return fail(RT_ERR_ARG, "bad argument");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(RT_ERR_CUDA, "no CUDA device available (this library has no CPU path)"); }
+  struct Buf { void* p = nullptr; ~Buf() { if (p) cudaFree(p); } } dx, dy, dout;
+  CU(cudaMalloc(&dx.p, (size_t)n * 8)); CU(cudaMalloc(&dy.p, (size_t)n * 8)); CU(cudaMalloc(&dout.p, (size_t)n * 8));
+  CU(cudaMemcpy(dx.p, x, (size_t)n * 8, cudaMemcpyHostToDevice)); CU(cudaMemcpy(dy.p, y, (size_t)n * 8, cudaMemcpyHostToDevice));
+  cudaError_t ce = launchStrictMathEval(fn, n, (const double*)dx.p, (const double*)dy.p, (double*)dout.p, as_float, 0);
+  if (ce == cudaSuccess) ce = cudaMemcpy(out, dout.p, (size_t)n * 8, cudaMemcpyDeviceToHost);
+  if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("strict math eval: ") + cudaGetErrorString(ce));
+  return RT_OK;
+}
+
 void rt_shutdown(void) {
-  std::lock_guard<std::mutex> lk(g_mu);
-  g_scenes.clear();
+  {
+    std::lock_guard<std::mutex> lk(g_mu);
+    g_scenes.clear();
+  }
+  std::lock_guard<std::mutex> lk(g_multi.mu);
+  for (void* c : g_multi.comms) if (c && g_multi.commDestroy) g_multi.commDestroy(c);
+  g_multi.comms.clear(); g_multi.wantNccl = false; g_multi.defaultGpus = 1;
 }
 
 }  // extern "C"

@@ -6,7 +6,7 @@
 //                   walk the BVH together.
 //   traceKernel   : K1, `hit world ray t_min t_max` for explicit rays with the visit log (parity probe).
 //   textureKernel : textureValue probe.   tonemapKernel : albedoToColor.
-// Included by rt_launch_exact.cu (--fmad=false, FAST=false) and rt_launch_fast.cu (FAST=true).
+// Included by rt_launch_exact.cu (--fmad=false, MODE 0), rt_launch_fast.cu (MODE 1) and rt_launch_strict.cu (--fmad=false, MODE 2).
 #pragma once
 #include <algorithm>
 #include <cstdlib>
@@ -26,20 +26,20 @@ template <> struct MinBlocks<double> { static constexpr int v = 1; };
 
 #include "rt_render_kernel.inl"
 
-template <class T>
+template <class T, int MODE>
 __global__ void textureKernel(const __grid_constant__ DScene<T> sc, uint32_t tex, uint32_t n, const double* q, double* out) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   Instr<0> ins;
   const double* a = q + (size_t)i * 5;
-  V3<T> c = textureValue<T, 0>(sc, tex, (T)a[0], (T)a[1], mk<T>((T)a[2], (T)a[3], (T)a[4]), ins);
+  V3<T> c = textureValue<T, 0, MODE>(sc, tex, (T)a[0], (T)a[1], mk<T>((T)a[2], (T)a[3], (T)a[4]), ins);
   out[i * 3] = c.x; out[i * 3 + 1] = c.y; out[i * 3 + 2] = c.z;
 }
 
 // ---- launchers -------------------------------------------------------------------------------------
-template <class T, class S, int INSTR, bool FAST>
+template <class T, class S, int INSTR, int MODE>
 static cudaError_t launchRenderT(const DScene<T>& sc, const RenderArgs& a, int stackDepth, int numSMs, cudaStream_t st, int* gridOut) {
-  auto kern = renderKernel<T, S, INSTR, FAST>;
+  auto kern = renderKernel<T, S, INSTR, MODE>;
   size_t smem = (size_t)columnWords<T>((uint32_t)stackDepth, a.lightCap) * kBlock * sizeof(uint32_t) + (kBlock / 32) * 16;  // columns + per-warp chunk slots
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
@@ -55,23 +55,22 @@ static cudaError_t launchRenderT(const DScene<T>& sc, const RenderArgs& a, int s
   return cudaGetLastError();
 }
 
-template <bool FAST>
+template <class T, class S, int MODE>
+static cudaError_t launchRenderI(int instr, const DScene<T>& sc, const RenderArgs& a, int stackDepth, int numSMs, cudaStream_t st, int* gridOut) {
+  if (instr == 1) return launchRenderT<T, S, 1, MODE>(sc, a, stackDepth, numSMs, st, gridOut);
+  if constexpr (MODE != MATH_FAST) { if (instr == 3) return launchRenderT<T, S, 3, MODE>(sc, a, stackDepth, numSMs, st, gridOut); }
+  return launchRenderT<T, S, 0, MODE>(sc, a, stackDepth, numSMs, st, gridOut);
+}
+template <int MODE>
 cudaError_t launchRender(int prec, int instr, const void* dscene, const RenderArgs& a, int stackDepth, int numSMs, cudaStream_t st, int* gridOut) {
-  if (prec == 0) {
-    const auto& sc = *static_cast<const DScene<float>*>(dscene);
-    return instr ? launchRenderT<float, float, 1, FAST>(sc, a, stackDepth, numSMs, st, gridOut) : launchRenderT<float, float, 0, FAST>(sc, a, stackDepth, numSMs, st, gridOut);
-  } else if (prec == 1) {
-    const auto& sc = *static_cast<const DScene<float>*>(dscene);
-    return instr ? launchRenderT<float, double, 1, FAST>(sc, a, stackDepth, numSMs, st, gridOut) : launchRenderT<float, double, 0, FAST>(sc, a, stackDepth, numSMs, st, gridOut);
-  } else {
-    const auto& sc = *static_cast<const DScene<double>*>(dscene);
-    return instr ? launchRenderT<double, double, 1, FAST>(sc, a, stackDepth, numSMs, st, gridOut) : launchRenderT<double, double, 0, FAST>(sc, a, stackDepth, numSMs, st, gridOut);
-  }
+  if (prec == 0) return launchRenderI<float, float, MODE>(instr, *static_cast<const DScene<float>*>(dscene), a, stackDepth, numSMs, st, gridOut);
+  if (prec == 1) return launchRenderI<float, double, MODE>(instr, *static_cast<const DScene<float>*>(dscene), a, stackDepth, numSMs, st, gridOut);
+  return launchRenderI<double, double, MODE>(instr, *static_cast<const DScene<double>*>(dscene), a, stackDepth, numSMs, st, gridOut);
 }
 
-template <class T, class S, bool FAST>
+template <class T, class S, int MODE>
 static cudaError_t launchTraceT(const DScene<T>& sc, const TraceArgs& a, int stackDepth, cudaStream_t st) {
-  auto kern = traceKernel<T, S, FAST>;
+  auto kern = traceKernel<T, S, MODE>;
   size_t smem = (size_t)(stackDepth + extraWords<T>()) * kBlock * sizeof(uint32_t);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
@@ -79,11 +78,18 @@ static cudaError_t launchTraceT(const DScene<T>& sc, const TraceArgs& a, int sta
   kern<<<(a.n + kBlock - 1) / kBlock, kBlock, smem, st>>>(sc, b);
   return cudaGetLastError();
 }
-template <bool FAST>
+template <int MODE>
 cudaError_t launchTrace(int prec, const void* dscene, const TraceArgs& a, int stackDepth, cudaStream_t st) {
-  if (prec == 0) return launchTraceT<float, float, FAST>(*static_cast<const DScene<float>*>(dscene), a, stackDepth, st);
-  if (prec == 1) return launchTraceT<float, double, FAST>(*static_cast<const DScene<float>*>(dscene), a, stackDepth, st);
-  return launchTraceT<double, double, FAST>(*static_cast<const DScene<double>*>(dscene), a, stackDepth, st);
+  if (prec == 0) return launchTraceT<float, float, MODE>(*static_cast<const DScene<float>*>(dscene), a, stackDepth, st);
+  if (prec == 1) return launchTraceT<float, double, MODE>(*static_cast<const DScene<float>*>(dscene), a, stackDepth, st);
+  return launchTraceT<double, double, MODE>(*static_cast<const DScene<double>*>(dscene), a, stackDepth, st);
+}
+
+template <int MODE>
+cudaError_t launchTexture(int prec, const void* dscene, uint32_t tex, uint32_t n, const double* q, double* out, cudaStream_t st) {
+  if (prec == 2) textureKernel<double, MODE><<<(n + 127) / 128, 128, 0, st>>>(*static_cast<const DScene<double>*>(dscene), tex, n, q, out);
+  else textureKernel<float, MODE><<<(n + 127) / 128, 128, 0, st>>>(*static_cast<const DScene<float>*>(dscene), tex, n, q, out);
+  return cudaGetLastError();
 }
 
 }  // namespace rtb

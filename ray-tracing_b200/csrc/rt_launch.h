@@ -20,6 +20,7 @@ struct RenderArgs {
   unsigned long long* counter;     // device: next free path index
   unsigned long long* ctr;         // device: 16 algorithmic-work counters (INSTR=1) or null
   double* out;                     // device: double[H*W*3] radiance sums, accumulated with atomicAdd
+  uint32_t* plogPrim; double* plogT; uint32_t plogStride;  // INSTR=3: per-path bounce log [total_paths][plogStride]
 };
 
 struct TraceArgs {
@@ -33,10 +34,14 @@ struct TraceArgs {
 };
 
 // prec: 0 fp32, 1 mixed, 2 fp64 ; dscene points at a host copy of DScene<float> (prec 0/1) or DScene<double> (2)
-template <bool FAST> cudaError_t launchRender(int prec, int instr, const void* dscene, const RenderArgs& a, int stackDepth, int numSMs, cudaStream_t st, int* gridOut);
-template <bool FAST> cudaError_t launchTrace(int prec, const void* dscene, const TraceArgs& a, int stackDepth, cudaStream_t st);
-cudaError_t launchTexture(int prec, const void* dscene, uint32_t tex, uint32_t n, const double* q, double* out, cudaStream_t st);
+// MODE: 0 literal arithmetic (rt_launch_exact.cu), 1 fast math (rt_launch_fast.cu), 2 strict math (rt_launch_strict.cu); instr: 0, 1 (counters), 3 (path log)
+template <int MODE> cudaError_t launchRender(int prec, int instr, const void* dscene, const RenderArgs& a, int stackDepth, int numSMs, cudaStream_t st, int* gridOut);
+template <int MODE> cudaError_t launchTrace(int prec, const void* dscene, const TraceArgs& a, int stackDepth, cudaStream_t st);
+template <int MODE> cudaError_t launchTexture(int prec, const void* dscene, uint32_t tex, uint32_t n, const double* q, double* out, cudaStream_t st);
+cudaError_t launchStrictMathEval(uint32_t fn, uint32_t n, const double* x, const double* y, double* out, int as_float, cudaStream_t st);
 cudaError_t launchDivSelftest(unsigned long long n, unsigned long long seed, unsigned long long* out2, cudaStream_t st);
+// dst[i] += src[0][i] + ... + src[n-1][i] (left to right), src may be peer-device memory (NVLink loads)
+cudaError_t launchReducePeer(double* dst, const double* const* src, int n, size_t elems, int numSMs, cudaStream_t st);
 cudaError_t launchTonemap(const double* sum, uint32_t n, double ns, uint8_t* out, cudaStream_t st);
 
 }  // namespace rtb

@@ -38,14 +38,10 @@ cudaError_t launchDivSelftest(unsigned long long n, unsigned long long seed, uns
   return cudaGetLastError();
 }
 
-template cudaError_t launchRender<false>(int, int, const void*, const RenderArgs&, int, int, cudaStream_t, int*);
-template cudaError_t launchTrace<false>(int, const void*, const TraceArgs&, int, cudaStream_t);
+template cudaError_t launchRender<MATH_LITERAL>(int, int, const void*, const RenderArgs&, int, int, cudaStream_t, int*);
+template cudaError_t launchTrace<MATH_LITERAL>(int, const void*, const TraceArgs&, int, cudaStream_t);
+template cudaError_t launchTexture<MATH_LITERAL>(int, const void*, uint32_t, uint32_t, const double*, double*, cudaStream_t);
 
-cudaError_t launchTexture(int prec, const void* dscene, uint32_t tex, uint32_t n, const double* q, double* out, cudaStream_t st) {
-  if (prec == 2) textureKernel<double><<<(n + 127) / 128, 128, 0, st>>>(*static_cast<const DScene<double>*>(dscene), tex, n, q, out);
-  else textureKernel<float><<<(n + 127) / 128, 128, 0, st>>>(*static_cast<const DScene<float>*>(dscene), tex, n, q, out);
-  return cudaGetLastError();
-}
 cudaError_t launchTonemap(const double* sum, uint32_t n, double ns, uint8_t* out, cudaStream_t st) {
   tonemapKernel<<<(n + 255) / 256, 256, 0, st>>>(sum, n, ns, out);
   return cudaGetLastError();

@@ -3,6 +3,6 @@
 #include "rt_kernels.cuh"
 
 namespace rtb {
-template cudaError_t launchRender<true>(int, int, const void*, const RenderArgs&, int, int, cudaStream_t, int*);
-template cudaError_t launchTrace<true>(int, const void*, const TraceArgs&, int, cudaStream_t);
+template cudaError_t launchRender<MATH_FAST>(int, int, const void*, const RenderArgs&, int, int, cudaStream_t, int*);
+template cudaError_t launchTrace<MATH_FAST>(int, const void*, const TraceArgs&, int, cudaStream_t);
 }  // namespace rtb

@@ -39,20 +39,21 @@ template <class T> RTB_D void accFlush(Trav<T>& tr, double* out) {
 
 // consume the finished query of this lane.  Returns true when a new query must be started on ray (qo, qd); its root is
 // world_root in phase PH_MAIN and the light in slot X_CURLIGHT in phase PH_LPDF.
-template <class T, int INSTR>
+template <class T, int INSTR, int MODE>
 __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, PathState<T>& ps, Instr<INSTR>& ins, V3<T>& qo, V3<T>& qd) {
   bool scattered = false;  // the path continues with (qo, qd) as the next bounce ray
   qo = tr.o; qd = tr.d;    // all frames are closed when a query ends: this is the query's world ray
   {
-    if (!tr.qhit()) { accAdd<T>(tr, ps.beta * mk<T>(sc.bg[0], sc.bg[1], sc.bg[2])); ps.phase = PH_IDLE; return false; }  // Lib.hs:1310-1313
+    if (!tr.qhit()) { ins.bounce(kNone, 0.0); accAdd<T>(tr, ps.beta * mk<T>(sc.bg[0], sc.bg[1], sc.bg[2])); ps.phase = PH_IDLE; return false; }  // Lib.hs:1310-1313
+    ins.bounce(tr.bprim, (double)tr.tbest);
     HitRec<T> rec;
-    evalHit<T>(sc, tr.o, tr.d, ps.time, tr.tbest, tr.bprim, tr.baux(), tr.bdepth(), &tr.xu(X_BCHAIN), tr.stride * (uint32_t)(sizeof(T) / 4), rec);
+    evalHit<T, MODE>(sc, tr.o, tr.d, ps.time, tr.tbest, tr.bprim, tr.baux(), tr.bdepth(), &tr.xu(X_BCHAIN), tr.stride * (uint32_t)(sizeof(T) / 4), rec);
     const Q4<T> m = ldq(sc.mats + rec.mat);
     const uint32_t mkind = bitsOf(m.x), tex = bitsOf(m.y);
     // the material's texture, evaluated at ONE call site (textureValue draws no random numbers, so its position relative to the
     // samplers below is free): not needed by Dielectric (white) and by a light seen from its front face (black)
     V3<T> tv = mk<T>(0, 0, 0);
-    if (mkind != M_DIELECTRIC && !(mkind == M_LIGHT && rec.front)) tv = textureValue<T, INSTR>(sc, tex, rec.u, rec.v, rec.p, ins);
+    if (mkind != M_DIELECTRIC && !(mkind == M_LIGHT && rec.front)) tv = textureValue<T, INSTR, MODE>(sc, tex, rec.u, rec.v, rec.p, ins);
     if (mkind == M_LIGHT) {  // scatter = Nothing -> emitted, back face only (Lib.hs:860, 880-885)
       accAdd<T>(tr, ps.beta * tv); ps.phase = PH_IDLE;
       return false;
@@ -60,8 +61,8 @@ __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, Path
       const Onb<T> uvw = onbFromW(rec.n);
       const T rd = rnd<T>(ps.rng);
       V3<T> pdfD;
-      if (rd < (T)0.5) pdfD = htblRandom<T>(sc, sc.lights_root, rec.p, ps.rng);
-      else pdfD = onbLocal(uvw, randomCosineDirection<T>(ps.rng));
+      if (rd < (T)0.5) pdfD = htblRandom<T, MODE>(sc, sc.lights_root, rec.p, ps.rng);
+      else pdfD = onbLocal(uvw, randomCosineDirection<T, MODE>(ps.rng));
       const V3<T> dir = unit(pdfD);
       const T cosine = dot(unit(dir), uvw.w);
       const T v2 = (cosine <= 0) ? (T)0 : cosine / kPi<T>();
@@ -81,7 +82,7 @@ __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, Path
         return true;
       }
     } else if (mkind == M_METAL) {  // Lib.hs:837-841: never absorbs, fuzz unclamped
-      const V3<T> rUnit = randomUnitVector<T>(ps.rng);
+      const V3<T> rUnit = randomUnitVector<T, MODE>(ps.rng);
       const V3<T> reflected = reflectV(unit(tr.d), rec.n);
       ps.beta = ps.beta * tv;
       qo = rec.p; qd = reflected + scale(m.z, rUnit);
@@ -117,7 +118,7 @@ __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, Path
 // (walked depth-first, left first), then start the query of the next light on the same ray, or — all lights done — weight the
 // throughput (Lib.hs:1329-1333) and start the bounce's `hit world`.  Runs right after the traversal step that finished the query
 // (not through the shade class): the lane stays in the traversal classes.
-template <class T, int INSTR, bool FAST>
+template <class T, int INSTR, int MODE>
 RTB_D void lpdfAdvance(const DScene<T>& sc, Trav<T>& tr, PathState<T>& ps, Instr<INSTR>& ins, uint32_t lbase, uint32_t lightCap) {
   const uint32_t curLight = tr.xu(X_CURLIGHT);
   const T curW = xld<T>(tr, X_CURW);
@@ -164,16 +165,17 @@ RTB_D void lpdfAdvance(const DScene<T>& sc, Trav<T>& tr, PathState<T>& ps, Instr
     ins.count(1);
   }
   ins.count(13);
-  travBegin<T, FAST>(sc, tr, root, qo, qd, kEps<T>(), kInf<T>());
+  travBegin<T, MODE>(sc, tr, root, qo, qd, kEps<T>(), kInf<T>());
 }
 
-template <class T, class S, int INSTR, bool FAST>
+template <class T, class S, int INSTR, int MODE>
 __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __grid_constant__ DScene<T> sc, const __grid_constant__ RenderArgs a) {
   extern __shared__ uint32_t smem[];
   const unsigned lane = threadIdx.x & 31u;
   const unsigned ltMask = (1u << lane) - 1u;
   Instr<INSTR> ins;
   if constexpr (INSTR == 1) ins.init();
+  if constexpr (INSTR == 3) ins.init(a.plogPrim, a.plogT, a.plogStride);
 
   Trav<T> tr;
   tr.col = smem + threadIdx.x;
@@ -226,20 +228,20 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
       }
     }
     if (pick == 0) {
-      if (isNode) stepNode<T, INSTR, FAST>(sc, tr, ins);
+      if (isNode) stepNode<T, INSTR, MODE>(sc, tr, ins);
     } else if (pick == 1) {
       if (isLeaf) stepSphere<T, S, INSTR>(sc, tr, (ps.phase == PH_MAIN) ? ps.time : (T)0, ins);  // htblPdfValue traces with time 0 (Lib.hs:677)
     } else if (pick == 2) {
       if (cls == 2) stepRect<T, INSTR>(sc, tr, ins);
     } else if (pick == 3) {
-      if (cls == 3) stepRare<T, INSTR, FAST>(sc, tr, ps.rng, ins);
+      if (cls == 3) stepRare<T, INSTR, MODE>(sc, tr, ps.rng, ins);
     }
     if (pick != 4) {
-      if (ps.phase == PH_LPDF && tr.cur == kEmpty) lpdfAdvance<T, INSTR, FAST>(sc, tr, ps, ins, a.stackCap + (uint32_t)extraWords<T>(), a.lightCap);
+      if (ps.phase == PH_LPDF && tr.cur == kEmpty) lpdfAdvance<T, INSTR, MODE>(sc, tr, ps, ins, a.stackCap + (uint32_t)extraWords<T>(), a.lightCap);
     } else {
       // ---- shade class: (1) consume finished queries
       bool start = false; V3<T> qo = tr.o, qd = tr.d;
-      if (cls == 4 && ps.phase != PH_IDLE) start = shadeStep<T, INSTR>(sc, tr, ps, ins, qo, qd);
+      if (cls == 4 && ps.phase != PH_IDLE) start = shadeStep<T, INSTR, MODE>(sc, tr, ps, ins, qo, qd);
       // ---- (2) path regeneration: idle lanes take the next path indices of the warp's chunk, in lane order
       unsigned idle = __ballot_sync(0xffffffffu, cls == 4 && ps.phase == PH_IDLE);
       while (idle) {
@@ -269,6 +271,7 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
           }
           ps.rng = streamGen(a.seed, pixel, s);
           ins.count(0);
+          ins.beginPath((unsigned long long)pl * a.ns + off % a.ns);
           // uniformRandomUVs (Lib.hs:1362-1365): u = (x + ru)/W, v = (y + rv)/H with y counted from the bottom row
           const T ru = rnd<T>(ps.rng), rv = rnd<T>(ps.rng);
           const T u = ((T)col + ru) / (T)a.W, v = ((T)(a.H - 1 - row) + rv) / (T)a.H;
@@ -295,7 +298,7 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
       if (start) {
         ins.count(13);
         if (ps.phase == PH_MAIN) ins.count(1);
-        travBegin<T, FAST>(sc, tr, ps.phase == PH_MAIN ? sc.world_root : tr.xu(X_CURLIGHT), qo, qd, kEps<T>(), kInf<T>());
+        travBegin<T, MODE>(sc, tr, ps.phase == PH_MAIN ? sc.world_root : tr.xu(X_CURLIGHT), qo, qd, kEps<T>(), kInf<T>());
       } else if (cls == 4) {
         tr.cur = kDead;  // only reached when the index space is exhausted
       }
@@ -309,7 +312,7 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
 }
 
 // K1: one ray per thread, the same step functions run to completion, with the visit log
-template <class T, class S, bool FAST>
+template <class T, class S, int MODE>
 __global__ void __launch_bounds__(kBlock) traceKernel(const __grid_constant__ DScene<T> sc, const __grid_constant__ TraceArgs a) {
   extern __shared__ uint32_t smem[];
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -322,14 +325,14 @@ __global__ void __launch_bounds__(kBlock) traceKernel(const __grid_constant__ DS
   for (uint32_t k = 0; k < a.logStride; ++k) a.vlog[(size_t)i * a.logStride + k] = kNone;
   Trav<T> tr;
   tr.col = smem + threadIdx.x;
-  travBegin<T, FAST>(sc, tr, sc.world_root, o, d, (T)a.tmin, (T)a.tmax);
-  travRun<T, S, 2, FAST>(sc, tr, time, rng, ins);
+  travBegin<T, MODE>(sc, tr, sc.world_root, o, d, (T)a.tmin, (T)a.tmax);
+  travRun<T, S, 2, MODE>(sc, tr, time, rng, ins);
   a.nvisit[i] = ins.n; a.vhash[i] = ins.h;
   a.hit[i] = tr.qhit() ? 1 : 0;
   double* out = a.rec + (size_t)i * 9;
   if (tr.qhit()) {
     HitRec<T> rec;
-    evalHit<T>(sc, o, d, time, tr.tbest, tr.bprim, tr.baux(), tr.bdepth(), &tr.xu(X_BCHAIN), tr.stride * (uint32_t)(sizeof(T) / 4), rec);
+    evalHit<T, MODE>(sc, o, d, time, tr.tbest, tr.bprim, tr.baux(), tr.bdepth(), &tr.xu(X_BCHAIN), tr.stride * (uint32_t)(sizeof(T) / 4), rec);
     out[0] = rec.t; out[1] = rec.p.x; out[2] = rec.p.y; out[3] = rec.p.z; out[4] = rec.n.x; out[5] = rec.n.y; out[6] = rec.n.z; out[7] = rec.u; out[8] = rec.v;
     a.prim[i] = tr.bprim; a.mat[i] = rec.mat; a.front[i] = rec.front ? 1 : 0;
   } else {

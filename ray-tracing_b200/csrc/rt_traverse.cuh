@@ -91,8 +91,8 @@ RTB_D void axisMode(float d, bool oSafe, float& r, uint32_t& mode) {
   else { r = 0.0f; mode = 2u; }
 }
 // per-ray (per frame) setup of the slab test's divisions
-template <class T, bool FAST> RTB_D void setInv(const DScene<T>& sc, Trav<T>& tr) {
-  if constexpr (FAST) {
+template <class T, int MODE> RTB_D void setInv(const DScene<T>& sc, Trav<T>& tr) {
+  if constexpr (MODE == MATH_FAST) {
     tr.inv = mk<T>((T)1 / tr.d.x, (T)1 / tr.d.y, (T)1 / tr.d.z);
   } else if constexpr (sizeof(T) == 4) {
     const bool oSafe = !sc.bigCoords && !(tr.flags & F_NANT) && fabsf(tr.o.x) <= kDivHi && fabsf(tr.o.y) <= kDivHi && fabsf(tr.o.z) <= kDivHi;
@@ -103,10 +103,10 @@ template <class T, bool FAST> RTB_D void setInv(const DScene<T>& sc, Trav<T>& tr
 }
 
 // start `hit root (Ray o d _) t_min t_max`
-template <class T, bool FAST>
+template <class T, int MODE>
 RTB_D void travBegin(const DScene<T>& sc, Trav<T>& tr, uint32_t root, const V3<T>& o, const V3<T>& d, T t_min, T t_max) {
   tr.o = o; tr.d = d; tr.flags = (t_max == t_max) ? 0u : F_NANT;
-  setInv<T, FAST>(sc, tr);
+  setInv<T, MODE>(sc, tr);
   tr.tmin = t_min; tr.tbest = t_max; tr.cur = root; tr.bprim = 0; tr.sp = 0;
 }
 
@@ -124,7 +124,7 @@ template <class T> RTB_D void travAccept(Trav<T>& tr, T t, uint32_t ref, uint32_
   }
 }
 
-template <class T, int INSTR, bool FAST>
+template <class T, int INSTR, int MODE>
 RTB_D void stepNode(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
   const uint32_t idx = tr.cur & kIdxMask;
   ins.visit(tr.cur); ins.boxTest();
@@ -138,7 +138,7 @@ RTB_D void stepNode(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
     else { tr.push(bitsOf(hi.w)); tr.cur = lc; }
   };
   bool pass;
-  if constexpr (!FAST && sizeof(T) == 4) {
+  if constexpr (MODE != MATH_FAST && sizeof(T) == 4) {
     bool ok = (tr.flags & F_MODE_GENERIC) == 0u;  // no axis in the generic division mode
     const bool bx = slabHoisted(lo.x, hi.x, tr.o.x, tr.d.x, tr.inv.x, tr.tmin, tr.tbest, ok);
     const bool by = slabHoisted(lo.y, hi.y, tr.o.y, tr.d.y, tr.inv.y, tr.tmin, tr.tbest, ok);
@@ -153,9 +153,9 @@ RTB_D void stepNode(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
       return;
     }
   } else {
-    const bool bx = slab<T, FAST>(lo.x, hi.x, tr.o.x, tr.d.x, tr.inv.x, tr.tmin, tr.tbest);
-    const bool by = slab<T, FAST>(lo.y, hi.y, tr.o.y, tr.d.y, tr.inv.y, tr.tmin, tr.tbest);
-    const bool bz = slab<T, FAST>(lo.z, hi.z, tr.o.z, tr.d.z, tr.inv.z, tr.tmin, tr.tbest);
+    const bool bx = slab<T, MODE == MATH_FAST>(lo.x, hi.x, tr.o.x, tr.d.x, tr.inv.x, tr.tmin, tr.tbest);
+    const bool by = slab<T, MODE == MATH_FAST>(lo.y, hi.y, tr.o.y, tr.d.y, tr.inv.y, tr.tmin, tr.tbest);
+    const bool bz = slab<T, MODE == MATH_FAST>(lo.z, hi.z, tr.o.z, tr.d.z, tr.inv.z, tr.tmin, tr.tbest);
     pass = bx && by && bz;
   }
   if (pass) descend(); else tr.next();
@@ -226,16 +226,16 @@ RTB_D void stepRect(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
 }
 
 // restore the current-frame ray after a frame exit: the saved world ray, then replay the chain of still-open frames
-template <class T, bool FAST> RTB_D void travReframe(const DScene<T>& sc, Trav<T>& tr) {
+template <class T, int MODE> RTB_D void travReframe(const DScene<T>& sc, Trav<T>& tr) {
   const int fd = tr.fd();
   tr.o = mk<T>(xld<T>(tr, X_WORLD + 0), xld<T>(tr, X_WORLD + 1), xld<T>(tr, X_WORLD + 2));
   tr.d = mk<T>(xld<T>(tr, X_WORLD + 3), xld<T>(tr, X_WORLD + 4), xld<T>(tr, X_WORLD + 5));
   for (int i = 0; i < fd; ++i) applyXform<T>(sc, tr.xu(X_CHAIN + i), tr.o, tr.d);
-  setInv<T, FAST>(sc, tr);
+  setInv<T, MODE>(sc, tr);
 }
 
 // the rare kinds: frames, markers, media, Unhittable
-template <class T, int INSTR, bool FAST>
+template <class T, int INSTR, int MODE>
 RTB_D void stepRare(const DScene<T>& sc, Trav<T>& tr, Rng& rng, Instr<INSTR>& ins) {
   const uint32_t ref = tr.cur, kind = ref >> 28, idx = ref & kIdxMask;
   if (kind == K_TRANSLATE || kind == K_ROTATE) {
@@ -249,12 +249,12 @@ RTB_D void stepRare(const DScene<T>& sc, Trav<T>& tr, Rng& rng, Instr<INSTR>& in
     tr.xu(X_CHAIN + fd) = ref;
     tr.setFd(fd + 1);
     applyXform<T>(sc, ref, tr.o, tr.d);
-    setInv<T, FAST>(sc, tr);
+    setInv<T, MODE>(sc, tr);
     tr.push(K_MARK_FRAME << 28);
     tr.cur = child;
   } else if (kind == K_MARK_FRAME) {
     tr.setFd(tr.fd() - 1);
-    travReframe<T, FAST>(sc, tr);
+    travReframe<T, MODE>(sc, tr);
     tr.next();
   } else if (kind == K_MEDIUM) {  // Lib.hs:1054: hit boundary ray (-inf) inf
     ins.visit(ref);
@@ -287,7 +287,7 @@ RTB_D void stepRare(const DScene<T>& sc, Trav<T>& tr, Rng& rng, Instr<INSTR>& in
         const T rayLength = len(tr.d);
         const T distInside = (rec2t - rec1t) * rayLength;
         const T xi = rnd<T>(rng);
-        const T hitDist = ldq(sc.media + idx).x * mlog(xi);
+        const T hitDist = ldq(sc.media + idx).x * mlog<MODE>(xi);
         if (!(hitDist > distInside)) travAccept<T>(tr, rec1t + (hitDist / rayLength), (K_MEDIUM << 28) | idx, 0);
       }
     }
@@ -305,14 +305,14 @@ RTB_D int stepClass(uint32_t cur) {
 }
 
 // run a whole query to completion (K1 and the texture-free probes): same steps, no scheduling
-template <class T, class S, int INSTR, bool FAST>
+template <class T, class S, int INSTR, int MODE>
 RTB_D void travRun(const DScene<T>& sc, Trav<T>& tr, T time, Rng& rng, Instr<INSTR>& ins) {
   while (tr.cur != kEmpty) {
     const int c = stepClass(tr.cur);
-    if (c == 0) stepNode<T, INSTR, FAST>(sc, tr, ins);
+    if (c == 0) stepNode<T, INSTR, MODE>(sc, tr, ins);
     else if (c == 1) stepSphere<T, S, INSTR>(sc, tr, time, ins);
     else if (c == 2) stepRect<T, INSTR>(sc, tr, ins);
-    else stepRare<T, INSTR, FAST>(sc, tr, rng, ins);
+    else stepRare<T, INSTR, MODE>(sc, tr, rng, ins);
   }
 }
 

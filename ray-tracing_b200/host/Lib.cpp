@@ -4,6 +4,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <stdexcept>
@@ -378,11 +379,20 @@ std::vector<std::vector<RGB>> runRender(const RenderStaticEnv& env, std::vector<
   if (gens.empty()) throw std::runtime_error("runRender: no generators");
   Arena::Flat flat;
   env.arena->flatten(env.scene.world, env.scene.lights, env.scene.background, env.camera, flat);
+  // The reference parallelises inside runRender (sparks over the pixels of a row, Lib.hs:1519-1520); the drop-in shards inside
+  // rt_render over every visible GPU.  RTB_GPUS=n pins the count (1 = single device); decided once per process.
+  static const int gpus = [] {
+    const char* v = std::getenv("RTB_GPUS");
+    const int want = v ? std::atoi(v) : 0;
+    return (rt_device_count() > 1 && want != 1) ? rt_init(want, 0) : 1;
+  }();
+  (void)gpus;
   rt_scene_t sc = 0;
   if (rt_scene_create(&flat.desc, -1, &sc) != RT_OK) throw std::runtime_error(std::string("rt_scene_create: ") + rt_last_error());
   RtRenderParams p{};
   p.width = (uint32_t)env.width; p.height = (uint32_t)env.height; p.sample_offset = 0; p.sample_count = (uint32_t)env.numSamples;
-  p.total_samples = (uint32_t)env.numSamples; p.max_depth = (uint32_t)env.maxDepth; p.seed = genWord64(gens[0]); p.precision = RT_PREC_F32; p.device = -1;
+  p.total_samples = (uint32_t)env.numSamples; p.max_depth = (uint32_t)env.maxDepth; p.seed = genWord64(gens[0]); p.precision = RT_PREC_DEFAULT; p.device = -1;
+  p.n_gpus = 0;  // the library default: one device, or what rt_init(n) set (all the box's GPUs for rt_init(0))
   std::vector<double> sums((size_t)env.width * env.height * 3, 0.0);
   const int rc = rt_render(sc, &p, sums.data(), nullptr);
   const std::string err = rc == RT_OK ? "" : rt_last_error();

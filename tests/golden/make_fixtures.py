@@ -1,8 +1,10 @@
 """Regenerates the committed fixtures under tests/golden/ from the reference's data files.
 
 Run in the build container only (needs /root/reference and PIL); the GPU box uses the committed outputs.
-  earthmap_rgb8.npz        : /root/reference/earthmap.jpg decoded to RGB8 (PIL; the reference decodes the same file with
-                             JuicyPixels, Scenes.hs:157-165 — decoder differences of +-1 LSB are possible)
+  ../../ray-tracing_b200/data/earthmap_rgb8.npz
+                           : /root/reference/earthmap.jpg decoded to RGB8 (PIL; the reference decodes the same file with
+                             JuicyPixels, Scenes.hs:157-165 — decoder differences of +-1 LSB are possible).  It is
+                             an INPUT of the product (the image texture of three scenes), so it lives in the package, not here
   cornellBox1000_box4.npy  : /root/reference/cornellBox1000.png (500x500, the HEAD Main.hs configuration) as 8-bit values
                              box-averaged 4x4 -> float32 [125,125,3]; the loose statistical golden for config 4
 """
@@ -13,7 +15,7 @@ from PIL import Image
 here = os.path.dirname(os.path.abspath(__file__))
 ref = "/root/reference"
 earth = np.asarray(Image.open(os.path.join(ref, "earthmap.jpg")).convert("RGB"), dtype=np.uint8)
-np.savez_compressed(os.path.join(here, "earthmap_rgb8.npz"), rgb=earth)
+np.savez_compressed(os.path.join(here, "..", "..", "ray-tracing_b200", "data", "earthmap_rgb8.npz"), rgb=earth)
 png = np.asarray(Image.open(os.path.join(ref, "cornellBox1000.png")).convert("RGB"), dtype=np.float32)
 assert png.shape == (500, 500, 3)
 box = png.reshape(125, 4, 125, 4, 3).mean(axis=(1, 3)).astype(np.float32)

@@ -3,11 +3,16 @@ on the same seeded inputs.
 
 Bars (north_star):
   * hit ids, hit t and BVH traversal order: BIT-EXACT — fp64 kernels vs oracle<double> (= the reference's arithmetic) and
-    fp32 kernels vs oracle<float>, on a fixed ray set (pixel-centre primary rays + seeded random rays);
-  * radiance: per-(pixel,sample) streams are shared with the oracle, so images are compared pixel-for-pixel.  Tolerance:
-    at least 90 % of pixels within 1e-3 relative (paths only separate where libm/CUDA transcendentals differ in the last
-    ulp and flip a comparison) and the image mean within 2 %; fp32 vs the reference's Double additionally by converged-mean
-    RMSE against the oracle's own seed-to-seed noise floor.
+    fp32 / mixed kernels vs oracle<float> / oracle<float,double>, on a fixed ray set (pixel-centre primary rays + seeded random rays),
+    up to 90 000 spheres (cfg5 scale);
+  * radiance with the PRODUCTION transcendentals (libdevice on the device, glibc in the oracle): per-(pixel,sample) streams are
+    shared, so images are compared pixel-for-pixel.  fp64: >= 99.9 % of pixels within 1e-12 (observed 100 %, profiles/
+    r2_parity_fractions.json).  fp32 / mixed: >= 90 % within 1e-3 and the mean within 2 % — a last-ulp difference of a scattered
+    direction changes the rounding of the next hit point, which decides the t_min = 1e-4 self-intersection test (Lib.hs:77, 1309), so
+    ~0.3 % of fp32 paths separate (tools/parity_classify.py).  With the shared strict-math functions nothing separates:
+    tests/test_gpu_strict.py holds the same comparisons to 99.9 % within 1e-6 / 1e-12;
+  * the production arithmetic (RT_PREC_MIXED) vs the reference's Double by converged means against the oracle's own seed-to-seed
+    noise floor, on cfg1-4 scenes.
 """
 import numpy as np
 import pytest
@@ -76,6 +81,27 @@ def test_trace_bit_exact(gpu, O, oracle_scene, dev_scene, name, prec):
     assert g["hit"].sum() > 100
 
 
+@pytest.mark.parametrize("prec", ["f64", "f32", "mixed"])
+def test_trace_bit_exact_90k_spheres(gpu, O, prec):
+    """cfg5-scale traversal parity: the synthetic sphere grid at synth_n = 300 (90 000 spheres + 2 rects behind makeBVH, 131 071
+    nodes, 18 levels): hit, primitive, t / p / normal and the visit count + hash of ~80 000 `hit` calls per ray, bit-exact on
+    2 400 + 600 rays.  (The reference's independent-axis box test makes the visit count linear in N)"""
+    gp, op = {"f64": (gpu.PREC_F64, O.PREC_F64), "f32": (gpu.PREC_F32, O.PREC_F32), "mixed": (gpu.PREC_MIXED, O.PREC_MIXED)}[prec]
+    osc = O.OracleScene("synthetic", synth_n=300)
+    rays = _rays(O, osc, n_rand=600)
+    if prec != "f64":
+        rays = rays.astype(np.float32).astype(np.float64)
+    hs = gpu.HostScene("synthetic", synth_n=300)
+    ds = hs.upload(W, H)
+    g = ds.trace(rays, precision=gp, seed=9, log_stride=64)
+    ds.destroy()
+    o = osc.trace(rays, prec=op, seed=9, log_stride=64)
+    assert len(rays) >= 2000 and o["nvisit"].mean() > 20000
+    for k in ("hit", "prim", "mat", "front", "nvisit", "vhash", "vlog"):
+        assert np.array_equal(g[k], o[k]), k
+    assert np.array_equal(g["rec"][:, :7], o["rec"][:, :7])
+
+
 @pytest.mark.parametrize("name", NO_MEDIA)
 def test_fp32_traversal_agrees_with_reference_double(gpu, O, oracle_scene, dev_scene, name):
     """fp32 device traversal vs the reference's Double arithmetic: agreement rate of hit id and visit order (grazing rays differ)."""
@@ -113,37 +139,45 @@ def _cmp_images(img, ref, frac_min=0.90, mean_tol=0.02):
 
 
 @pytest.mark.parametrize("name,lit", [(n, False) for n in ALL] + [(n, True) for n in ALL if n not in ("cornell", "cornell_smoke", "synthetic")])
-def test_render_matches_oracle_same_streams(gpu, O, oracle_scene, dev_scene, name, lit):
-    """K2 fp32 vs oracle<float>, identical per-(pixel,sample) streams, 8 spp, depth 50."""
+@pytest.mark.parametrize("prec", ["mixed", "f32"])
+def test_render_matches_oracle_same_streams(gpu, O, oracle_scene, dev_scene, name, lit, prec):
+    """K2 (production transcendentals) vs the oracle (glibc) in the same arithmetic, identical per-(pixel,sample) streams, 8 spp, depth 50."""
     spp = 8
-    img, st = dev_scene(name, lit).render(W, H, spp, depth=50, seed=21)
-    ref, _ = oracle_scene(name, lit).render(W, H, spp, depth=50, prec=O.PREC_F32, mode=1, seed=21)
+    gp, op = {"f32": (gpu.PREC_F32, O.PREC_F32), "mixed": (gpu.PREC_MIXED, O.PREC_MIXED)}[prec]
+    img, st = dev_scene(name, lit).render(W, H, spp, depth=50, seed=21, precision=gp)
+    ref, _ = oracle_scene(name, lit).render(W, H, spp, depth=50, prec=op, mode=1, seed=21)
     assert st["samples"] == W * H * spp and st["launches"] == 1
     media = name in ("cornell_smoke", "next_week_final")
     _cmp_images(img, ref, frac_min=0.80 if media else 0.90, mean_tol=0.04 if media else 0.02)
 
 
-@pytest.mark.parametrize("name", ["cornell", "random", "next_week_final"])
-def test_render_fp64_matches_reference_arithmetic(gpu, O, oracle_scene, dev_scene, name):
-    """K2 in fp64 vs oracle<double> — the reference's own arithmetic — same streams."""
-    lit = name != "cornell"
-    img, _ = dev_scene(name, lit).render(W, H, 4, depth=50, seed=33, precision=gpu.PREC_F64)
-    ref, _ = oracle_scene(name, lit).render(W, H, 4, depth=50, prec=O.PREC_F64, mode=1, seed=33)
-    _cmp_images(img, ref, frac_min=0.85 if name == "next_week_final" else 0.93, mean_tol=0.03)
+@pytest.mark.parametrize("name,lit", [(n, False) for n in ALL] + [(n, True) for n in ("random_book1", "random", "next_week_final")])
+def test_render_fp64_matches_reference_arithmetic(gpu, O, oracle_scene, dev_scene, name, lit):
+    """K2 in fp64 vs oracle<double> IN THE REFERENCE'S OWN FORM (multiply-on-return throughput chain, glibc transcendentals), same
+    streams: identical NaN masks and >= 99.9 % of pixels within 1e-12 (observed: all; r2_parity_fractions.json)."""
+    img, _ = dev_scene(name, lit).render(W, H, 8, depth=50, seed=33, precision=gpu.PREC_F64)
+    ref, _ = oracle_scene(name, lit).render(W, H, 8, depth=50, prec=O.PREC_F64, mode=1, seed=33)
+    ng, nr = np.isnan(img).any(axis=2), np.isnan(ref).any(axis=2)
+    assert np.array_equal(ng, nr)
+    ok = ~ng
+    if ok.any():
+        rel = (np.abs(img[ok] - ref[ok]) / (np.abs(ref[ok]) + 1e-3)).max(axis=1)
+        assert (rel < 1e-12).mean() >= 0.999, (float((rel < 1e-12).mean()), float(rel.max()))
 
 
-@pytest.mark.parametrize("name", ["cornell", "simple_light", "random_book1"])
-def test_radiance_vs_reference_double_converged(gpu, O, oracle_scene, dev_scene, name):
-    """GPU vs the reference's Double at matched spp, on the same and on independent streams.  The production arithmetic (fp32 with the sphere quadratic
-    in fp64, RT_PREC_MIXED) must sit at the oracle's own seed-to-seed noise floor (RMSE of converged means <= 1.25 x floor, mean
-    within 1.5 %).  Pure fp32 is allowed the self-intersection darkening that a radius-1000 sphere causes with t_min = 1e-4
-    (Lib.hs:77,1309): mean within 8 %."""
-    lit = name != "cornell"
+@pytest.mark.parametrize("name,lit", [("cornell", False), ("simple_light", True), ("random_book1", True), ("random", True), ("next_week_final", True)])
+def test_radiance_vs_reference_double_converged(gpu, O, oracle_scene, dev_scene, name, lit):
+    """The DEFAULT arithmetic of the product (RT_PREC_DEFAULT = fp32 with the sphere quadratic in fp64: what runRender, the Haskell
+    binding and bench.py use) vs the reference's Double at matched spp, on the same and on independent streams, on cfg4, a light
+    scene and the lit cfg1 / cfg2 / cfg3: RMSE of the converged means <= 1.25 x the oracle's own seed-to-seed floor, paired RMSE
+    <= 0.6 x floor, mean within 1.5 %.  Pure fp32 (opt-in) is only held to 8 % on the mean: its sphere quadratic re-hits a
+    radius-1000 sphere from its own surface at t_min = 1e-4 (Lib.hs:77, 1309), which darkens every Book-1/2 scene."""
     spp = 256
     w, h = 48, 32
+    assert gpu.PREC_DEFAULT == gpu.PREC_MIXED
     hs = gpu.HostScene(name, lit=lit)
     ds = hs.upload(w, h)
-    gm, _ = ds.render(w, h, spp, seed=101, precision=gpu.PREC_MIXED)
+    gm, _ = ds.render(w, h, spp, seed=101)  # the default precision
     gf, _ = ds.render(w, h, spp, seed=101, precision=gpu.PREC_F32)
     ds.destroy()
     osc = oracle_scene(name, lit)
@@ -156,7 +190,7 @@ def test_radiance_vs_reference_double_converged(gpu, O, oracle_scene, dev_scene,
     gm, gf, a, b = (np.minimum(x[ok] / spp, 4.0) for x in (gm, gf, a, b))  # clip fireflies symmetrically
     floor = np.sqrt(np.mean((a - b) ** 2))
     assert np.sqrt(np.mean((gm - b) ** 2)) < 1.25 * floor, (np.sqrt(np.mean((gm - b) ** 2)), floor)
-    # same streams: fp32+fp64-sphere tracks the reference's Double far below the Monte-Carlo noise
+    # same streams: the production arithmetic tracks the reference's Double far below the Monte-Carlo noise
     assert np.sqrt(np.mean((gm - a) ** 2)) < 0.6 * floor, (np.sqrt(np.mean((gm - a) ** 2)), floor)
 
     def mean_ok(x, tol):  # paired difference of means: within tol, or statistically indistinguishable (|z| < 4) in a heavy-tailed scene
@@ -167,10 +201,11 @@ def test_radiance_vs_reference_double_converged(gpu, O, oracle_scene, dev_scene,
 
 
 def test_counters_equal_oracle_traversal_counts(gpu, O, oracle_scene, dev_scene):
-    """The algorithmic-work counters behind the roofline (box tests, primitive tests, bounces ...) are the oracle's, exactly, when
-    every path coincides; scenes without transcendentals on the path (two_spheres lit is not one) so compare within 1 %."""
+    """The algorithmic-work counters behind the roofline (box tests, primitive tests, bounces ...) with the production transcendentals:
+    within 1 % of the oracle's (the few fp32 paths that separate, see the module docstring).  EXACT equality is asserted where every
+    path coincides: tests/test_gpu_strict.py::test_strict_counters_exactly_equal."""
     for name, lit in (("cornell", False), ("random_book1", True)):
-        _, st = dev_scene(name, lit).render(W, H, 4, counted=True, seed=77)
+        _, st = dev_scene(name, lit).render(W, H, 4, counted=True, seed=77, precision=gpu.PREC_F32)
         _, os_ = oracle_scene(name, lit).render(W, H, 4, prec=O.PREC_F32, mode=1, seed=77, stats=True)
         c = st["counters"]
         assert c["paths"] == os_["paths"] == W * H * 4
@@ -282,8 +317,8 @@ def test_hoisted_reciprocal_division_is_ieee(gpu):
 @pytest.mark.parametrize("name,w,h", [("random", 600, 400), ("cornell", 500, 500), ("next_week_final", 400, 400)])
 def test_full_size_properties(gpu, O, earth, name, w, h):
     """BASELINE.json's full image sizes: (i) the frame is the sum of its sample slices and of its row bands (what spp / tile
-    sharding relies on), to double round-off; (ii) at 2 spp the image matches the oracle on the same streams like the small
-    cases do (NaN masks, >= 90 % of pixels within 1e-3, mean within 2 %; media scene 80 % / 4 %)."""
+    sharding relies on), to double round-off; (ii) at 2 spp, in the production arithmetic with strict math, the full-size image
+    matches the oracle on the same streams like the small cases do (identical NaN masks, >= 99.9 % of pixels within 1e-6)."""
     hs = gpu.HostScene(name)
     ds = hs.upload(w, h)
     full, st = ds.render(w, h, 6, seed=11)
@@ -296,12 +331,14 @@ def test_full_size_properties(gpu, O, earth, name, w, h):
     top = np.zeros((h, w, 3)); ds.render(w, h, 6, seed=11, region=(0, h // 3, 0, w), out=top)
     bot = np.zeros((h, w, 3)); ds.render(w, h, 6, seed=11, region=(h // 3, h, 0, w), out=bot)
     assert np.allclose((top + bot)[~nan], full[~nan], rtol=1e-12, atol=1e-12)
-    img, _ = ds.render(w, h, 2, seed=17)
+    img, _ = ds.render(w, h, 2, seed=17, flags=gpu.FLAG_STRICT_MATH)
     ds.destroy()
     osc = O.OracleScene(name, earth=earth if name in EARTH_SCENES else None)
-    ref, _ = osc.render(w, h, 2, depth=50, prec=O.PREC_F32, mode=1, seed=17)
-    media = name == "next_week_final"
-    _cmp_images(img, ref, frac_min=0.80 if media else 0.90, mean_tol=0.04 if media else 0.02)
+    ref, _ = osc.render(w, h, 2, depth=50, prec=O.PREC_MIXED, mode=1, seed=17, strict=True, order="beta")
+    ng, nr = np.isnan(img).any(axis=2), np.isnan(ref).any(axis=2)
+    assert np.array_equal(ng, nr)
+    rel = (np.abs(img[~ng] - ref[~ng]) / (np.abs(ref[~ng]) + 1e-3)).max(axis=1)
+    assert (rel < 1e-6).mean() >= 0.999, float((rel < 1e-6).mean())
 
 
 # ---- makeBVH on the device (rt_bvh_build)

@@ -20,7 +20,7 @@ def test_abi_exports_every_declared_symbol(R):
     L = R.core()
     for s in declared:
         assert hasattr(L, s), s
-    assert L.rt_abi_version() == 1
+    assert L.rt_abi_version() == 2
     lim = R.RtLimits()
     assert L.rt_get_limits(C.byref(lim)) == 0 and lim.max_frames >= 2 and lim.max_stack >= 48
 
@@ -171,7 +171,7 @@ def _mini_desc(R, keep, **kw):
                   tex_scale=np.ones(1, f))
     arrays.update({k: v for k, v in kw.items() if isinstance(v, np.ndarray)})
     d = R.RtSceneDesc()
-    d.abi_version = 1
+    d.abi_version = 2
     counts = dict(n_spheres="sphere_mat", n_materials="mat_kind", n_textures="tex_kind", n_nodes="node_left", n_translates="translate_child",
                   n_rotates="rotate_child", n_media="medium_mat", n_rects="rect_mat", n_cuboids="cuboid_mat", n_moving="moving_mat")
     for cnt, arr in counts.items():

@@ -176,7 +176,7 @@ typedef struct RtStats {
   double h2d_ms, d2h_ms;   /* copies inside this call (0 for the *_device entry points) */
   uint64_t samples;        /* camera paths traced by this call */
   uint64_t launches;       /* kernels launched by this call */
-  uint64_t counters[16];   /* RT_CTR_* when the call was made with counters enabled, else 0 */
+  uint64_t counters[24];   /* RT_CTR_* when the call was made with counters enabled, else 0 */
   uint64_t sched[16];      /* warp-scheduler statistics of the instrumented kernel: [0..4] iterations that ran class c (node, sphere,
                               rect, rare, shade), [5..9] lanes served by them, [10..14] lanes waiting per class summed over all
                               iterations, [15] iterations */
@@ -185,6 +185,8 @@ typedef struct RtStats {
   uint32_t gpus;           /* devices that rendered a share of this call (1 for single-device calls) */
   uint32_t reduce_kind;    /* RT_REDUCE_* actually used */
   double gpu_kernel_ms[16];/* per device share: kernel time (kernel_ms is their maximum) */
+  double tail_ms;          /* the persistent kernel's drain: from the first warp that found the path index space empty to the exit of
+                              the last warp (device globaltimer; the maximum over the devices of a multi-GPU call) */
 } RtStats;
 enum RtReduceKind { RT_REDUCE_NONE = 0, RT_REDUCE_PEER = 1 /* one kernel on the scene's device reading the peers' framebuffers over NVLink */,
                     RT_REDUCE_NCCL = 2 /* ncclReduce(sum) onto the scene's device */, RT_REDUCE_STAGED = 3 /* no peer access: cudaMemcpyPeer + add */ };
@@ -192,7 +194,11 @@ enum RtReduceKind { RT_REDUCE_NONE = 0, RT_REDUCE_PEER = 1 /* one kernel on the 
 enum RtCounter { RT_CTR_PATHS = 0, RT_CTR_BOUNCES = 1, RT_CTR_BOX_TESTS = 2, RT_CTR_SPHERE_TESTS = 3, RT_CTR_MOVING_TESTS = 4,
                  RT_CTR_RECT_TESTS = 5, RT_CTR_CUBOID_TESTS = 6, RT_CTR_TRANSLATE = 7, RT_CTR_ROTATE = 8, RT_CTR_MEDIUM = 9,
                  RT_CTR_SPHERE_HITS = 10, RT_CTR_NOISE_CALLS = 11, RT_CTR_TEXELS = 12, RT_CTR_QUERIES = 13, RT_CTR_VISITS = 14,
-                 RT_CTR_UNHITTABLE = 15 };
+                 RT_CTR_UNHITTABLE = 15,
+                 /* shading events (the "+ shading" term of SURVEY 8d's flop count): scatter by material (Lib.hs:822-865), emitted
+                    (880-885), htblRandom on the light list (707-724), htblPdfValue leaf formulas (673-705), checker levels (498-501) */
+                 RT_CTR_SCATTER_LAMBERTIAN = 16, RT_CTR_SCATTER_METAL = 17, RT_CTR_SCATTER_DIELECTRIC = 18, RT_CTR_SCATTER_ISOTROPIC = 19,
+                 RT_CTR_EMITTED = 20, RT_CTR_LIGHT_SAMPLES = 21, RT_CTR_LIGHT_PDF_LEAVES = 22, RT_CTR_CHECKER_EVALS = 23 };
 
 typedef struct RtLimits {
   uint32_t max_stack;        /* traversal stack entries per path the kernels can be launched with */

@@ -17,7 +17,8 @@ KIND_NAMES = ["Unhittable", "Sphere", "MovingSphere", "RectXY", "RectXZ", "RectY
               "Rotate", "ConstantMedium"]
 STAT_NAMES = ["paths", "bounces", "box_tests", "sphere_tests", "moving_tests", "rect_tests", "cuboid_tests",
               "translate_visits", "rotate_visits", "medium_visits", "sphere_hits", "noise_calls", "texels", "queries",
-              "visits", "unhittable_visits"]
+              "visits", "unhittable_visits", "scatter_lambertian", "scatter_metal", "scatter_dielectric", "scatter_isotropic",
+              "emitted", "light_samples", "light_pdf_leaves", "checker_evals"]
 
 
 def build(force=False):
@@ -123,7 +124,7 @@ class OracleScene:
         cam = self.camera(W, H) if cam is None else np.ascontiguousarray(cam, dtype=np.float64)
         r0, r1, c0, c1 = region if region else (0, H, 0, W)
         threads = threads or os.cpu_count() or 1
-        out = np.zeros((H, W, 3)); st = np.zeros(16, np.uint64)
+        out = np.zeros((H, W, 3)); st = np.zeros(24, np.uint64)
         flags = (1 if strict else 0) | (2 if order == "beta" else 0)
         if (flags or pathlog) and mode != 1:
             raise ValueError("strict / beta / pathlog need mode=1")

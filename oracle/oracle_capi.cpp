@@ -28,6 +28,7 @@ void statsOut(const Trace& t, uint64_t* s) {
   s[5] = t.prim[Hittable::RectXY] + t.prim[Hittable::RectXZ] + t.prim[Hittable::RectYZ]; s[6] = t.prim[Hittable::Cuboid];
   s[7] = t.prim[Hittable::Translate]; s[8] = t.prim[Hittable::Rotate]; s[9] = t.prim[Hittable::ConstantMedium];
   s[10] = t.sphereHits; s[11] = t.noiseCalls; s[12] = t.texels; s[13] = t.queries; s[14] = t.nVisit; s[15] = t.prim[Hittable::Unhittable];
+  for (int i = 0; i < 8; ++i) s[16 + i] = t.shade[i];
 }
 
 template <class T, class S>
@@ -177,14 +178,14 @@ int orc_trace(void* p, int prec, int flags, int n, const double* rays7, double t
 
 // mode 0: reference RNG plumbing (runRender, per-column SplitMix; `seed` stands in for Main's entropy);
 // mode 1: per-(pixel,sample) streams (the product's RNG), region/sample-range restricted.
-// out: double[H*W*3] radiance SUMS, row 0 = top.  stats16 may be null.
+// out: double[H*W*3] radiance SUMS, row 0 = top.  stats24 may be null.
 // flags / path log (mode 1 only): see orc_trace; pathPrim / pathT: [paths][pathStride] or null
 int orc_render(void* p, const double* cam24, int prec, int W, int H, int s0, int ns, int maxDepth, int mode, uint64_t seed, int row0, int row1,
-               int col0, int col1, int nThreads, double* out, uint64_t* stats16, int flags, uint32_t* pathPrim, double* pathT, uint32_t pathStride) {
+               int col0, int col1, int nThreads, double* out, uint64_t* stats24, int flags, uint32_t* pathPrim, double* pathT, uint32_t pathStride) {
   try {
     Scene& s = ((Handle*)p)->scene;
     Camera cam = cameraFrom24(cam24);
-    bool st = stats16 != nullptr;
+    bool st = stats24 != nullptr;
     RenderOut r;
     if (mode == 0) {
       if (prec == 0) r = renderReference<float, float>(s, cam, W, H, ns, maxDepth, seed, nThreads, st);
@@ -197,7 +198,7 @@ int orc_render(void* p, const double* cam24, int prec, int W, int H, int s0, int
       else r = renderStreams<double, double>(s, cam, W, H, s0, ns, maxDepth, seed, row0, row1, col0, col1, nThreads, st, strict, beta, pathPrim, pathT, pathStride);
     }
     std::memcpy(out, r.sum.data(), r.sum.size() * sizeof(double));
-    statsOut(r.stats, stats16);
+    statsOut(r.stats, stats24);
     return 0;
   } catch (const std::exception& e) { g_err = e.what(); return -1; }
 }

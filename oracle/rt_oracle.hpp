@@ -406,6 +406,9 @@ struct Trace {
   uint64_t nVisit = 0, visitHash = 0xcbf29ce484222325ULL;
   // counters (BASELINE.md "algorithmic work"): box tests, primitive tests by kind, sphere hit records, bounces
   uint64_t boxTests = 0, prim[Hittable::NKinds] = {0}, sphereHits = 0, bounces = 0, paths = 0, noiseCalls = 0, texels = 0, queries = 0;
+  // shading events: [0..3] scatter Lambertian / Metal / Dielectric / Isotropic, [4] emitted, [5] htblRandom on the light list,
+  // [6] htblPdfValue leaf formulas evaluated, [7] checker levels evaluated
+  uint64_t shade[8] = {0};
   // per-path log of the main queries (rayColor's `hit world`), bounce order: (prim ref | 0xffffffff = miss, t) — same definition as
   // the device's rt_render_pathlog; filled when pathPrim != nullptr
   uint32_t* pathPrim = nullptr; double* pathT = nullptr; uint32_t pathStride = 0, pathBounce = 0;
@@ -420,6 +423,7 @@ struct Trace {
     boxTests += o.boxTests; sphereHits += o.sphereHits; bounces += o.bounces; paths += o.paths; noiseCalls += o.noiseCalls;
     texels += o.texels; queries += o.queries; nVisit += o.nVisit;
     for (int i = 0; i < Hittable::NKinds; ++i) prim[i] += o.prim[i];
+    for (int i = 0; i < 8; ++i) shade[i] += o.shade[i];
   }
 };
 
@@ -644,6 +648,7 @@ template <class T, class S> struct Tracer {
     switch (tex->kind) {
       case Texture::Constant: return Vec3<T>((T)tex->rgb[0], (T)tex->rgb[1], (T)tex->rgb[2]);
       case Texture::Checker:
+        if (tr) ++tr->shade[7];
         if (msin(10 * p.x) * msin(10 * p.y) * msin(10 * p.z) < 0) return textureValue(tex->odd.get(), u, v, p);
         return textureValue(tex->even.get(), u, v, p);
       case Texture::Perlin: {
@@ -669,12 +674,14 @@ template <class T, class S> struct Tracer {
     if (!hit(h, Ray<T>{origin, v, (T)0.0}, K<T>::epsilon(), K<T>::infinity(), rec)) return 0;
     switch (h->kind) {
       case Hittable::RectXZ: {
+        if (tr) ++tr->shade[6];
         T area = ((T)h->a1 - (T)h->a0) * ((T)h->b1 - (T)h->b0);
         T distanceSquared = rec.t * rec.t * squaredLength(v);
         T cosine = std::fabs(dot(v, rec.normal) / length(v));
         return distanceSquared / (cosine * area);
       }
       case Hittable::Sphere: {
+        if (tr) ++tr->shade[6];
         Vec3<T> center(h->c0); T radius = (T)h->r;
         T cosThetaMax = std::sqrt(1 - radius * radius / squaredLength(center - origin));
         T solidAngle = 2 * K<T>::pi() * (1 - cosThetaMax);
@@ -733,11 +740,13 @@ template <class T, class S> struct Tracer {
   bool scatter(const Material* m, const Ray<T>& r, const Hit<T>& h, ScatterRecord& s) {  // 822-865
     switch (m->kind) {
       case Material::Lambertian: {
+        if (tr) ++tr->shade[0];
         Vec3<T> att = textureValue(m->tex.get(), h.u, h.v, h.p);
         const Hittable* lights = sc.lights.get();
         ONB<T> uvw = onbFromW(h.normal);
         // pdfGenerate (MixturePdf lightsPdf cosinePdf)  367-372
         T rd = rnd();
+        if (tr && rd < (T)0.5) ++tr->shade[5];
         Vec3<T> pdfD = (rd < (T)0.5) ? htblRandom(lights, h.p) : onbLocalV(uvw, randomCosineDirection());
         s.ray = Ray<T>{h.p, makeUnitVector(pdfD), r.time};
         // pdfValue mixPdf (makeUnitVector pdfD)  374-382
@@ -749,6 +758,7 @@ template <class T, class S> struct Tracer {
         return true;
       }
       case Material::Metal: {
+        if (tr) ++tr->shade[1];
         Vec3<T> rUnit = randomUnitVector();
         Vec3<T> reflected = reflect(makeUnitVector(r.d), h.normal);
         s.ray = Ray<T>{h.p, reflected + scale((T)m->param, rUnit), r.time};
@@ -756,6 +766,7 @@ template <class T, class S> struct Tracer {
         return true;
       }
       case Material::Dielectric: {
+        if (tr) ++tr->shade[2];
         T ref_idx = (T)m->param;
         T etaiOverEtat = h.frontFace ? (T)1.0 / ref_idx : ref_idx;
         Vec3<T> unitDirection = makeUnitVector(r.d);
@@ -767,8 +778,9 @@ template <class T, class S> struct Tracer {
         else s.ray = Ray<T>{h.p, refract(unitDirection, h.normal, etaiOverEtat), r.time};
         return true;
       }
-      case Material::DiffuseLight: return false;
+      case Material::DiffuseLight: if (tr) ++tr->shade[4]; return false;
       default: {  // Isotropic 861-865
+        if (tr) ++tr->shade[3];
         Vec3<T> randDr = randomInUnitSphere();
         s.ray = Ray<T>{h.p, randDr, r.time};
         s.att = textureValue(m->tex.get(), h.u, h.v, h.p);

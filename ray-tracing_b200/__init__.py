@@ -26,7 +26,8 @@ KIND_NAMES = ["Unhittable", "Sphere", "MovingSphere", "RectXY", "RectXZ", "RectY
               "Rotate", "ConstantMedium"]
 COUNTER_NAMES = ["paths", "bounces", "box_tests", "sphere_tests", "moving_tests", "rect_tests", "cuboid_tests",
                  "translate_visits", "rotate_visits", "medium_visits", "sphere_hits", "noise_calls", "texels", "queries",
-                 "visits", "unhittable_visits"]
+                 "visits", "unhittable_visits", "scatter_lambertian", "scatter_metal", "scatter_dielectric", "scatter_isotropic",
+                 "emitted", "light_samples", "light_pdf_leaves", "checker_evals"]
 SCENES = ["cornell", "cornell_smoke", "simple_light", "earth", "two_perlin", "two_spheres", "random_book1", "random",
           "next_week_final", "synthetic", "quirks"]
 
@@ -60,9 +61,9 @@ class RtRenderParams(C.Structure):
 
 class RtStats(C.Structure):
     _fields_ = [("kernel_ms", C.c_double), ("h2d_ms", C.c_double), ("d2h_ms", C.c_double), ("samples", C.c_uint64),
-                ("launches", C.c_uint64), ("counters", C.c_uint64 * 16), ("sched", C.c_uint64 * 16),
+                ("launches", C.c_uint64), ("counters", C.c_uint64 * 24), ("sched", C.c_uint64 * 16),
                 ("reduce_ms", C.c_double), ("replicate_ms", C.c_double), ("gpus", C.c_uint32), ("reduce_kind", C.c_uint32),
-                ("gpu_kernel_ms", C.c_double * 16)]
+                ("gpu_kernel_ms", C.c_double * 16), ("tail_ms", C.c_double)]
 
 
 class RtLimits(C.Structure):

@@ -60,7 +60,7 @@ struct DeviceCtx {
   int device = 0, numSMs = 148;
   DevBuffers<float> f32;
   DevBuffers<double> f64;
-  unsigned long long* d_counter = nullptr;  // [0] path counter, [1..16] work counters, [17..32] scheduler statistics
+  unsigned long long* d_counter = nullptr;  // kCtrTotal words: [0] path counter, work counters, scheduler statistics, tail stamps (rt_device.cuh kCtr*)
   double* d_fb = nullptr; size_t fbElems = 0;
   cudaStream_t stream = nullptr;            // multi-GPU shares only (the single-device entry points use the caller's / default stream)
   cudaEvent_t evStart = nullptr, evDone = nullptr;
@@ -344,8 +344,8 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
   const void* dsc = nullptr;
   int rc = deviceScene(hs, c, q.precision, &dsc);
   if (rc) return rc;
-  if (!c->d_counter) { CU(cudaMalloc(&c->d_counter, 33 * sizeof(unsigned long long))); }
-  CU(cudaMemsetAsync(c->d_counter, 0, 33 * sizeof(unsigned long long), st));
+  if (!c->d_counter) { CU(cudaMalloc(&c->d_counter, kCtrTotal * sizeof(unsigned long long))); }
+  CU(cudaMemsetAsync(c->d_counter, 0, kCtrTotal * sizeof(unsigned long long), st));
   if (q.sample_count == 0) return RT_OK;
   RenderArgs a{};
   a.W = q.width; a.H = q.height; a.s0 = q.sample_offset; a.ns = q.sample_count; a.maxDepth = q.max_depth;
@@ -368,7 +368,7 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
   a.rareMin = std::max(1u, tuneParam("RTB_RARE_MIN", hs.n_media > 0 ? 4u : 8u));
   a.keepNode = std::max(1u, tuneParam("RTB_KEEP_NODE", 12)); a.keepLeaf = std::max(1u, tuneParam("RTB_KEEP_LEAF", 8));
   a.lightCap = hs.lightCap;
-  a.counter = c->d_counter; a.ctr = instr == 1 ? c->d_counter + 1 : nullptr; a.out = d_out;
+  a.counter = c->d_counter; a.ctr = instr == 1 ? c->d_counter + kCtrWorkBase : nullptr; a.out = d_out;
   if (plog) { a.plogPrim = plog->prim; a.plogT = plog->t; a.plogStride = plog->stride; }
   cudaError_t ce;
   if (q.flags & RT_FLAG_FAST_MATH) ce = launchRender<MATH_FAST>((int)q.precision, instr == 3 ? 0 : instr, dsc, a, hs.stackDepth, c->numSMs, st, gridOut);
@@ -540,6 +540,13 @@ int renderMulti(SceneEntry* e, const RtRenderParams& q, int nGpus, double* out, 
       if (k < 16) stats->gpu_kernel_ms[k] = ms;
       stats->kernel_ms = std::max(stats->kernel_ms, (double)ms);
     }
+    for (int k = 0; k < n; ++k) {
+      unsigned long long tt[2] = {0, 0};
+      CU(cudaSetDevice(devs[k]));
+      CU(cudaMemcpy(tt, ctx[k]->d_counter + kCtrTailBase, sizeof(tt), cudaMemcpyDeviceToHost));
+      if (tt[0] && tt[1] > tt[0]) stats->tail_ms = std::max(stats->tail_ms, (double)(tt[1] - tt[0]) * 1e-6);
+    }
+    CU(cudaSetDevice(root->device));
     cudaEventElapsedTime(&ms, evs.ev[0], evs.ev[1]); stats->reduce_ms = ms;
     cudaEventElapsedTime(&ms, evs.ev[1], evs.ev[2]); stats->d2h_ms = ms;
     stats->samples = (uint64_t)(q.row1 - q.row0) * (q.col1 - q.col0) * q.sample_count;
@@ -609,11 +616,13 @@ int renderHost(rt_scene_t scene, const RtRenderParams* params, double* out, RtSt
     stats->samples = (uint64_t)paths;
     stats->launches = q.sample_count ? 1 : 0;
     stats->gpus = 1;
+    unsigned long long cc[kCtrTotal];
+    CU(cudaMemcpy(cc, c->d_counter, sizeof(cc), cudaMemcpyDeviceToHost));
     if (instr == 1) {
-      unsigned long long cc[33];
-      CU(cudaMemcpy(cc, c->d_counter, sizeof(cc), cudaMemcpyDeviceToHost));
-      for (int i = 0; i < 16; ++i) { stats->counters[i] = cc[i + 1]; stats->sched[i] = cc[i + 17]; }
+      for (int i = 0; i < kWorkCounters; ++i) stats->counters[i] = cc[kCtrWorkBase + i];
+      for (int i = 0; i < kSchedCounters; ++i) stats->sched[i] = cc[kCtrSchedBase + i];
     }
+    if (cc[kCtrTailBase] && cc[kCtrTailBase + 1] > cc[kCtrTailBase]) stats->tail_ms = (double)(cc[kCtrTailBase + 1] - cc[kCtrTailBase]) * 1e-6;
   }
   return RT_OK;
 }

@@ -17,8 +17,8 @@ struct RenderArgs {
   uint32_t keepNode, keepLeaf;     // run a node / sphere step without a full vote when at least this many lanes wait for one
   unsigned long long seed;
   unsigned long long total_paths;  // region pixels * ns
-  unsigned long long* counter;     // device: next free path index
-  unsigned long long* ctr;         // device: 16 algorithmic-work counters (INSTR=1) or null
+  unsigned long long* counter;     // device: [0] next free path index ... [kCtrTailBase], [+1] globaltimer stamps of the tail (rt_device.cuh kCtr*)
+  unsigned long long* ctr;         // device: kWorkCounters algorithmic-work counters + kSchedCounters scheduler statistics (INSTR=1) or null
   double* out;                     // device: double[H*W*3] radiance sums, accumulated with atomicAdd
   uint32_t* plogPrim; double* plogT; uint32_t plogStride;  // INSTR=3: per-path bounce log [total_paths][plogStride]
 };

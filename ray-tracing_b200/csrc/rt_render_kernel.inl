@@ -19,6 +19,7 @@ template <class T> struct PathState {
   V3<T> beta; T time; int depthLeft; int phase; Rng rng;
 };
 
+RTB_D unsigned long long globalTimerNs() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 RTB_D double ldD(const uint32_t* p, uint32_t stride) { return __longlong_as_double((long long)((unsigned long long)p[0] | ((unsigned long long)p[stride] << 32))); }
 RTB_D void stD(uint32_t* p, uint32_t stride, double v) { unsigned long long b = (unsigned long long)__double_as_longlong(v); p[0] = (uint32_t)b; p[stride] = (uint32_t)(b >> 32); }
 
@@ -55,13 +56,15 @@ __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, Path
     V3<T> tv = mk<T>(0, 0, 0);
     if (mkind != M_DIELECTRIC && !(mkind == M_LIGHT && rec.front)) tv = textureValue<T, INSTR, MODE>(sc, tex, rec.u, rec.v, rec.p, ins);
     if (mkind == M_LIGHT) {  // scatter = Nothing -> emitted, back face only (Lib.hs:860, 880-885)
+      ins.count(20);
       accAdd<T>(tr, ps.beta * tv); ps.phase = PH_IDLE;
       return false;
     } else if (mkind == M_LAMBERTIAN) {  // Lib.hs:823-836 with pdfGenerate/pdfValue of the mixture (367-382)
+      ins.count(16);
       const Onb<T> uvw = onbFromW(rec.n);
       const T rd = rnd<T>(ps.rng);
       V3<T> pdfD;
-      if (rd < (T)0.5) pdfD = htblRandom<T, MODE>(sc, sc.lights_root, rec.p, ps.rng);
+      if (rd < (T)0.5) { ins.count(21); pdfD = htblRandom<T, MODE>(sc, sc.lights_root, rec.p, ps.rng); }
       else pdfD = onbLocal(uvw, randomCosineDirection<T, MODE>(ps.rng));
       const V3<T> dir = unit(pdfD);
       const T cosine = dot(unit(dir), uvw.w);
@@ -82,12 +85,14 @@ __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, Path
         return true;
       }
     } else if (mkind == M_METAL) {  // Lib.hs:837-841: never absorbs, fuzz unclamped
+      ins.count(17);
       const V3<T> rUnit = randomUnitVector<T, MODE>(ps.rng);
       const V3<T> reflected = reflectV(unit(tr.d), rec.n);
       ps.beta = ps.beta * tv;
       qo = rec.p; qd = reflected + scale(m.z, rUnit);
       scattered = true;
     } else if (mkind == M_DIELECTRIC) {  // Lib.hs:842-859: xi is always drawn
+      ins.count(18);
       const T eta = rec.front ? (T)1.0 / m.z : m.z;
       const V3<T> ud = unit(tr.d);
       const T cosTheta = hmin(dot(neg(ud), rec.n), (T)1.0);
@@ -98,6 +103,7 @@ __device__ __forceinline__ bool shadeStep(const DScene<T>& sc, Trav<T>& tr, Path
       qo = rec.p;
       scattered = true;
     } else {  // Isotropic (Lib.hs:861-865) weighted by the generic scatteringPdf / 1.0 (867-878, 1329-1333)
+      ins.count(19);
       const V3<T> randDr = randomInUnitSphere<T>(ps.rng);
       const T c2 = dot(rec.n, randDr);
       const T spdf = (c2 < 0) ? (T)0 : c2 / kPi<T>();
@@ -126,12 +132,14 @@ RTB_D void lpdfAdvance(const DScene<T>& sc, Trav<T>& tr, PathState<T>& ps, Instr
   if (tr.qhit()) {
     const uint32_t lk = curLight >> 28, li = curLight & kIdxMask;
     if (lk == K_RECT_XZ) {
+      ins.count(22);
       const Q4<T> ra = ldq(sc.rects + 2 * (size_t)li);
       const T area = (ra.y - ra.x) * (ra.w - ra.z);
       const T distanceSquared = tr.tbest * tr.tbest * sqlen(tr.d);
       const T cosine = mabs(tr.d.y / len(tr.d));  // |v . (0,+-1,0)| / |v|
       xst<T>(tr, X_LV1, xld<T>(tr, X_LV1) + curW * (distanceSquared / (cosine * area)));
     } else if (lk == K_SPHERE) {
+      ins.count(22);
       const Q4<T> q = ldq(sc.spheres + li);
       const T cosThetaMax = msqrt(1 - q.w * q.w / sqlen(mk<T>(q.x, q.y, q.z) - tr.o));
       const T solidAngle = 2 * kPi<T>() * (1 - cosThetaMax);
@@ -251,7 +259,10 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
           unsigned long long base = 0;
           if (lane == 0) base = atomicAdd(a.counter, (unsigned long long)a.chunk);
           base = __shfl_sync(0xffffffffu, base, 0);
-          if (base >= a.total_paths) { exhausted = true; break; }
+          if (base >= a.total_paths) {  // first warp to find the index space empty stamps the start of the kernel's tail (RtStats::tail_ms)
+            if (lane == 0) atomicCAS(a.counter + kCtrTailBase, 0ull, globalTimerNs());
+            exhausted = true; break;
+          }
           cNext = 0;
           cEnd = (base + a.chunk < a.total_paths) ? a.chunk : (uint32_t)(a.total_paths - base);
           if (lane == 0) { ws[0] = (uint32_t)(base / a.ns); ws[1] = (uint32_t)(base % a.ns); ws[3] = cEnd; }
@@ -305,9 +316,10 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
     }
   }
   accFlush<T>(tr, a.out);
+  if (lane == 0) atomicMax(a.counter + kCtrTailBase + 1, globalTimerNs());  // the last warp to leave ends the tail
   if constexpr (INSTR == 1) {
-    for (int i = 0; i < 16; ++i) if (ins.c[i]) atomicAdd(a.ctr + i, (unsigned long long)ins.c[i]);
-    if (lane == 0) for (int i = 0; i < 16; ++i) if (sch[i]) atomicAdd(a.ctr + 16 + i, sch[i]);
+    for (int i = 0; i < kWorkCounters; ++i) if (ins.c[i]) atomicAdd(a.ctr + i, (unsigned long long)ins.c[i]);
+    if (lane == 0) for (int i = 0; i < kSchedCounters; ++i) if (sch[i]) atomicAdd(a.ctr + kWorkCounters + i, sch[i]);
   }
 }
 

@@ -111,7 +111,8 @@ def test_strict_counters_exactly_equal(gpu, O, oracle_scene, dev_scene, name, li
     c = st["counters"]
     assert c["paths"] == os_["paths"] == W * H * 4
     for k in ("bounces", "box_tests", "sphere_tests", "moving_tests", "rect_tests", "cuboid_tests", "translate_visits", "rotate_visits", "medium_visits",
-              "sphere_hits", "noise_calls", "texels", "queries", "visits"):
+              "sphere_hits", "noise_calls", "texels", "queries", "visits", "unhittable_visits", "scatter_lambertian", "scatter_metal", "scatter_dielectric",
+              "scatter_isotropic", "emitted", "light_samples", "light_pdf_leaves", "checker_evals"):
         assert c[k] == os_[k], (name, k, c[k], os_[k])
 
 

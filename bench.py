@@ -1,12 +1,19 @@
 #!/usr/bin/env python
-"""bench.py — samples/s of the path-tracing hot path on N B200s (one process per GPU), see the contract in the task statement.
+"""bench.py — samples/s of the path-tracing hot path on N B200s, see the contract in the task statement.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--scene NAME] [--spp S] [--impl reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--scene NAME] [--spp S] [--impl reference] [--no-per-scene]
 
-A step = one full-frame render of `spp` camera samples per pixel per GPU (weak scaling: N GPUs render N*spp samples per
-pixel, their partial framebuffers are summed onto rank 0 by one NCCL reduce inside the timed region).
-Default workload = BASELINE.json configs[1]: `makeRandomScene earthTex 0 1 (randGen 1024)` + `randomSceneCamera (600,400)`
-(The Next Week BVH scene: moving spheres, checker + earthmap image textures, glass cuboid), HEAD semantics, depth 50.
+A step = one full-frame render of `spp` camera samples per pixel per GPU in the PRODUCTION arithmetic (RT_PREC_MIXED: fp32 with the
+sphere quadratic in fp64).  Headline workload = BASELINE.json configs[1]: `makeRandomScene earthTex 0 1 (randGen 1024)` +
+`randomSceneCamera (600,400)` (The Next Week BVH scene), HEAD semantics, depth 50, 1024 spp.  The one JSON line also carries a
+`per_scene` block — cfg1, cfg3, cfg4 and the bounded cfg5 samples (90 k and 1 M spheres), each with its own `roofline`,
+`cpu_baseline` and `e2e` — because the metric is samples/s PER SCENE.
+
+N > 1 (launched by torchrun, one rank per GPU): the headline `value` is weak scaling over torch.distributed (every rank renders
+`spp` samples per pixel, one NCCL reduce of the double framebuffers per step).  Rank 0 ALONE then drives the drop-in path — ONE
+rt_render call with n_gpus = N, the library shards and reduces over NVLink itself — for `e2e` (weak) and the `strong` block (the
+fixed 1024-spp frame split N ways, with reduce_ms / tail_ms / scene_create_ms), and `sharding_check` compares the N-GPU frame with
+the 1-GPU frame.
 """
 import argparse
 import json
@@ -25,34 +32,34 @@ SCENE_DOC = {
     "random_book1": "cfg1 In One Weekend final scene (makeRandomSceneBookOne, 600x400)",
     "random": "cfg2 The Next Week BVH scene (makeRandomScene: moving spheres, checker, earthmap, glass cuboid; 600x400)",
     "next_week_final": "cfg3 The Next Week final scene (box field, media, instanced sphere cluster; 400x400)",
-    "cornell": "cfg4 Rest of Your Life Cornell box, mixture-pdf light sampling (500x500)",
-    "synthetic": "cfg5 synthetic 1M spheres behind a host-built BVH; bounded sample 480x270 x 1 spp of the 3840x2160 x 1024 spp frame (the reference's independent-axis box test visits ~1.8M nodes+leaves per camera sample here)",
+    "cornell": "cfg4 Rest of Your Life Cornell box, mixture-pdf light sampling (500x500x1000 = app/Main.hs)",
+    "synthetic": "cfg5 synthetic sphere grid behind a host-built BVH; BOUNDED sample of the 3840x2160x1024-spp frame (the reference's independent-axis box test visits ~1.8 nodes+leaves per sphere per camera sample, so the stated frame is ~1.5e16 steps)",
 }
 SCENE_SIZE = {"random_book1": (600, 400), "random": (600, 400), "next_week_final": (400, 400), "cornell": (500, 500), "synthetic": (480, 270)}
 SCENE_SPP = {"random_book1": 1024, "random": 1024, "next_week_final": 256, "cornell": 1000, "synthetic": 1}
-FP32_PEAK_TFLOPS_NOMINAL = 148 * 128 * 2 * 1.965e9 / 1e12  # FFMA = 2 flop; no measured figure in MEASURED_PEAKS.json
+CPU_SPP = {"random": 100, "random_book1": 100, "cornell": 100, "next_week_final": 16, "synthetic": 1}
+FP32_NOMINAL_LANE_OPS = 148 * 128 * 1.965e9  # lane-instructions/s; fallback when profiles/fp32_peak.json is missing
 
 
-def measured_traffic(scene, W, H, spp):
-    """DRAM bytes of one renderKernel launch of exactly this workload, from the committed ncu capture (profiles/r1_traffic.json); None if not captured."""
+def _json(path):
     try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json"))).get(scene)
+        return json.load(open(os.path.join(ROOT, path)))
     except (OSError, ValueError):
         return None
-    if not t or (t["width"], t["height"], t["spp"]) != (W, H, spp):
-        return None
-    return t["dram_bytes_read"] + t["dram_bytes_write"]
 
 
-def peaks():
-    try:
-        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        return None
+def measured_traffic(scene, W, H, spp, synth_n):
+    """DRAM / L2 bytes of ONE renderKernel launch of exactly this workload from the committed ncu captures (profiles/r2_traffic.json,
+    falling back to round 1's cfg2 entry); None when this workload was not captured."""
+    for f in ("profiles/r2_traffic.json", "profiles/r1_traffic.json"):
+        t = (_json(f) or {}).get(scene if scene != "synthetic" else "synthetic_%d" % synth_n)
+        if t and (t["width"], t["height"], t["spp"]) == (W, H, spp):
+            return t
+    return None
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons sampled every 500 ms during the timed regions (each query can delay a kernel launch by tens of ms: the wall-clocked e2e loop sees that)."""
+    """nvidia-smi clocks + throttle reasons sampled every 500 ms during the timed regions."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, index):
@@ -81,31 +88,54 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
 
 
-def algorithmic_work(counters):
-    """bytes and FP ops per sample from reference-order traversal counts."""
-    c = counters
+# Shading flops per event (one op = one add / mul / div / compare / sqrt / transcendental, counted off the reference's formulas;
+# DESIGN.md 6 has the derivation): camera ray (Lib.hs:1253-1267, 1362-1365), Lambertian scatter incl. onbFromW, cosine direction,
+# mixture pdf value and the throughput update (823-836, 367-382, 1329-1333), Metal (837-841), Dielectric (842-859, 887-903), Isotropic
+# (861-878), emitted (880-885), htblRandom per light sample (707-724, rect/sphere mix), htblPdfValue per leaf (673-705), checker level
+# (498-501), Perlin noise call (441-484; turb's 7 calls per marble lookup are counted by noise_calls), image lookup (504-510).
+SHADE_FLOPS = {"paths": 50, "scatter_lambertian": 105, "scatter_metal": 42, "scatter_dielectric": 60, "scatter_isotropic": 36, "emitted": 3,
+               "light_samples": 40, "light_pdf_leaves": 20, "checker_evals": 9, "noise_calls": 146, "texels": 12}
+
+
+def algorithmic_work(c):
+    """bytes and FP ops per sample from reference-order traversal counts (+ the shading events)."""
     n = max(c["paths"], 1)
     byts = 32 * c["box_tests"] + 16 * c["sphere_tests"] + 48 * c["moving_tests"] + 32 * c["rect_tests"] + 32 * c["cuboid_tests"] + 16 * c["bounces"] \
         + 4 * c["texels"] + 8 * 16 * c["noise_calls"]
-    flops = 24 * c["box_tests"] + 32 * (c["sphere_tests"] + c["moving_tests"]) + 30 * c["sphere_hits"] + 12 * c["rect_tests"] + 72 * c["cuboid_tests"]
-    return byts / n, flops / n, {k: c[k] / n for k in ("bounces", "box_tests", "sphere_tests", "moving_tests", "rect_tests", "cuboid_tests", "queries")}
+    trav = 24 * c["box_tests"] + 32 * (c["sphere_tests"] + c["moving_tests"]) + 30 * c["sphere_hits"] + 12 * c["rect_tests"] + 72 * c["cuboid_tests"]
+    shade = sum(SHADE_FLOPS[k] * c[k] for k in SHADE_FLOPS)
+    keys = ("bounces", "box_tests", "sphere_tests", "moving_tests", "rect_tests", "cuboid_tests", "queries", "scatter_lambertian", "scatter_metal",
+            "scatter_dielectric", "scatter_isotropic", "emitted", "light_samples", "light_pdf_leaves", "noise_calls", "texels")
+    return dict(bytes=byts / n, flops=(trav + shade) / n, flops_traversal=trav / n, flops_shading=shade / n, per_sample={k: c[k] / n for k in keys})
 
 
 def scene_bytes(d):
     """bytes of the flattened scene description that cross host->device in rt_scene_create"""
-    n = 0
-    n += d.n_nodes * (48 + 12) + d.n_spheres * 36 + d.n_moving * 76 + d.n_rects * 44 + d.n_cuboids * 52 + d.n_translates * 28 + d.n_rotates * 24
-    n += d.n_media * 16 + d.n_materials * 16 + d.n_textures * 44 + d.n_perlin * (768 * 8 + 768 * 4)
     import ctypes as C
+    n = d.n_nodes * (48 + 12) + d.n_spheres * 36 + d.n_moving * 76 + d.n_rects * 44 + d.n_cuboids * 52 + d.n_translates * 28 + d.n_rotates * 24
+    n += d.n_media * 16 + d.n_materials * 16 + d.n_textures * 44 + d.n_perlin * (768 * 8 + 768 * 4)
     for i in range(d.n_images):
-        w = C.cast(d.image_w, C.POINTER(C.c_uint32))[i]; h = C.cast(d.image_h, C.POINTER(C.c_uint32))[i]
-        n += w * h * 3
+        n += C.cast(d.image_w, C.POINTER(C.c_uint32))[i] * C.cast(d.image_h, C.POINTER(C.c_uint32))[i] * 3
     return int(n)
+
+
+def cpu_sample(scene, W, H, synth_n, spp, seed, threads):
+    """(w, h, spp, seconds) of the oracle<double> in the reference's own RNG plumbing on a bounded sample of the workload"""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as O
+    import rtb200_loader
+    pkg = rtb200_loader.load()
+    earth = pkg.load_earth() if scene in ("earth", "random", "next_week_final") else None
+    osc = O.OracleScene(scene, earth=earth, synth_n=synth_n)
+    w, h = (W, H) if scene != "synthetic" else ((48, 27) if synth_n <= 300 else (24, 14))
+    t = time.time()
+    osc.render(w, h, spp, depth=50, prec=O.PREC_F64, mode=0, seed=seed, threads=threads)
+    return w, h, spp, time.time() - t, osc
 
 
 def run_reference(args, W, H, rank):
     """--impl reference: the reference's CPU algorithm (oracle<double>, runRender's per-column SplitMix plumbing) on the host cores.
-    The Haskell build itself cannot run here (no GHC on either box); see DESIGN.md."""
+    The Haskell build itself cannot run here (no GHC on either box); see DESIGN.md 9."""
     if rank != 0:
         return
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
@@ -135,6 +165,201 @@ def run_reference(args, W, H, rank):
         "gpu_launches": 0}))
 
 
+class Ctx:
+    pass
+
+
+def roofline_block(scene, W, H, spp, synth_n, work, kernel_ms, peaks, fp32, fast):
+    samples = W * H * spp
+    secs = kernel_ms / 1e3
+    tr = measured_traffic(scene, W, H, spp, synth_n)
+    hbm_peak = peaks["hbm_gbs"] if peaks else 6650.0
+    ach_gbs = work["bytes"] * samples / secs / 1e9
+    ach_tf = work["flops"] * samples / secs / 1e12
+    lane_peak = (fp32["fadd_fmul_lane_inst_per_s"] if fp32 else FP32_NOMINAL_LANE_OPS) / 1e12
+    ffma_peak = (fp32["ffma_tflops"] if fp32 else 2 * FP32_NOMINAL_LANE_OPS / 1e12)
+    mem = {"algorithmic_bytes_per_sample": work["bytes"], "algorithmic_gbs": ach_gbs, "hbm_peak_gbs": hbm_peak,
+           "hbm_peak_source": "MEASURED_PEAKS.json hbm_gbs (burst)" if peaks else "fallback 6.65 TB/s",
+           "l2_peak_gbs": fp32["l2_read_gbs"] if fp32 else None,
+           "dram_bytes_per_launch": (tr["dram_bytes_read"] + tr["dram_bytes_write"]) if tr else None,
+           "lts_bytes_per_launch": tr.get("lts_bytes") if tr else None}
+    if tr:
+        mem["dram_gbs"] = mem["dram_bytes_per_launch"] / secs / 1e9
+        mem["dram_frac_of_hbm_peak"] = mem["dram_gbs"] / hbm_peak
+        if tr.get("lts_bytes") and mem["l2_peak_gbs"]:
+            mem["l2_gbs"] = tr["lts_bytes"] / (tr.get("kernel_ms", kernel_ms) / 1e3) / 1e9
+            mem["l2_frac_of_l2_peak"] = mem["l2_gbs"] / mem["l2_peak_gbs"]
+    if scene == "synthetic":
+        # the one memory-side config: 1 M spheres = 33.5 MB of nodes + 16 MB of spheres, L2-resident on B200 (126 MB): node / leaf
+        # fetch bandwidth against the measured L2 and HBM peaks
+        return {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
+                "traffic": mem["dram_bytes_per_launch"], "kernel": "renderKernel", "kernel_ms": kernel_ms, "peak_source": mem["hbm_peak_source"],
+                "l2": {"achieved_algorithmic_gbs": ach_gbs, "peak": mem["l2_peak_gbs"], "frac": ach_gbs / mem["l2_peak_gbs"] if mem["l2_peak_gbs"] else None,
+                       "peak_source": "profiles/fp32_peak.json l2_read_gbs (tools/fp32_peak.cu, 48 MB buffer)"},
+                "memory": mem, "algorithmic_flops_per_sample": work["flops"], "per_sample": work["per_sample"],
+                "note": "scene is L2-resident: algorithmic node/leaf bytes are served by L1/L2, DRAM traffic is the measured `traffic`"}
+    return {"bound": "fp32-issue", "achieved": ach_tf, "peak": ffma_peak if fast else lane_peak, "unit": "TFLOP/s",
+            "frac": ach_tf / (ffma_peak if fast else lane_peak), "traffic": mem["dram_bytes_per_launch"],
+            "peak_source": ("profiles/fp32_peak.json (tools/fp32_peak.cu, measured on this pool's B200): " if fp32 else "nominal 148 SM x 128 lanes x 1.965 GHz: ") +
+                           ("FFMA issue rate x 2" if fast else "non-FMA FADD/FMUL issue rate, 1 flop per lane-instruction — the literal build is compiled --fmad=false, "
+                            "so no algorithmic op can ride an FMA"),
+            "frac_of_ffma_peak": ach_tf / ffma_peak, "ffma_peak_tflops": ffma_peak,
+            "kernel": "renderKernel", "kernel_ms": kernel_ms, "algorithmic_flops_per_sample": work["flops"],
+            "flops_traversal_per_sample": work["flops_traversal"], "flops_shading_per_sample": work["flops_shading"], "per_sample": work["per_sample"],
+            "memory": mem,
+            "note": "scene is L1/L2-resident; the binding limit is FP32/ALU issue under divergence (ncu: smsp__issue_active, "
+                    "smsp__thread_inst_executed_per_inst_executed in profiles/)"}
+
+
+def measure(cx, scene, spp, steps, warmup, synth_n=1000, size=None, cpu=True, e2e=True, label=None):
+    """One workload: device-timed value (weak scaling over torch.distributed when world > 1), kernel-only time, roofline, e2e through
+    the C ABI with host buffers, CPU baseline.  Returns the dict for the JSON line (rank 0) or None."""
+    import torch
+    import torch.distributed as dist
+    pkg, args = cx.pkg, cx.args
+    from ray_tracing_b200 import _dist
+    W, H = size or SCENE_SIZE[scene]
+    world, rank, dev, stream = cx.world, cx.rank, cx.dev, cx.stream
+    flags = pkg.FLAG_FAST_MATH if args.fast else 0
+    prec = args.precision
+    t0 = time.perf_counter()
+    hs = pkg.HostScene(scene, synth_n=synth_n)
+    desc = hs.desc(W, H)
+    host_build_s = time.perf_counter() - t0
+    ds = pkg.DeviceScene(desc, cx.local)
+    fb = torch.zeros((H, W, 3), dtype=torch.float64, device=dev)
+    total_spp = spp * world  # weak scaling: every GPU renders `spp` samples per pixel
+
+    work = None
+    if rank == 0:  # algorithmic work per sample (instrumented kernel, small spp; the counters equal the oracle's, tests/test_gpu_strict.py)
+        if scene == "synthetic":
+            _, st = ds.render(min(W, 96), min(H, 54), 1, counted=True, seed=99, precision=prec, flags=flags)
+        else:
+            _, st = ds.render(W, H, 2, counted=True, seed=99, precision=prec, flags=flags)
+        work = algorithmic_work(st["counters"])
+
+    def sync():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(i, ev=None):
+        cx.flush.zero_()  # L2 flush between iterations
+        fb.zero_()
+        s0, n = _dist.shard_samples(total_spp, rank, world)
+        if ev:
+            ev[0].record()
+        ds.render_device(fb.data_ptr(), W, H, n, stream=stream, depth=50, seed=1 + i, s0=s0, precision=prec, flags=flags, total=total_spp)
+        if ev:
+            ev[1].record()
+        _dist.reduce_framebuffer(fb, 0)
+
+    for i in range(warmup):
+        step(i)
+    sync()
+    k_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        step(100 + i, k_ev[i])
+    e1.record()
+    sync()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in k_ev]))
+    value = steps * W * H * total_spp / (ms / 1e3)
+    finite_frac = float(torch.isfinite(fb).all(dim=2).float().mean().item()) if rank == 0 else None
+
+    out = None
+    if rank == 0:
+        out = {"scene": scene, "workload": SCENE_DOC[scene] if scene != "synthetic" else SCENE_DOC[scene] + "; %d spheres, %dx%d x %d spp" % (synth_n * synth_n, W, H, spp),
+               "width": W, "height": H, "spp_per_gpu_per_step": spp, "steps": steps, "warmup": warmup,
+               "value": value, "unit": "samples/s", "ms_per_step": ms / steps, "kernel_ms": kernel_ms, "finite_pixel_fraction": finite_frac,
+               "roofline": roofline_block(scene, W, H, spp, synth_n, work, kernel_ms, cx.peaks, cx.fp32, args.fast), "gpu_launches": steps}
+        if scene == "synthetic":
+            out["host_scene_build_s"] = host_build_s
+
+    # ---- e2e: the user-facing call with HOST buffers.  N = 1: rt_scene_create (H2D) + rt_render (D2H of the frame inside), every step.
+    #      N > 1: rank 0 alone, ONE rt_render with n_gpus = N (scene replicated by the library on the first call, NVLink reduce, one D2H)
+    if e2e:
+        cx.cpu_barrier()
+        if rank == 0:
+            host_out = np.zeros((H, W, 3))
+            stats = []
+
+            def e2e_step(i, n_spp):
+                d2 = pkg.DeviceScene(desc, cx.local)
+                _, st = d2.render(W, H, n_spp, depth=50, seed=500 + i, out=host_out, precision=prec, flags=flags, n_gpus=world)
+                d2.destroy()
+                return st
+            e2e_step(0, total_spp)
+            t0 = time.perf_counter()
+            for i in range(steps):
+                stats.append(e2e_step(1 + i, total_spp))
+            e2e_s = time.perf_counter() - t0
+            out["e2e"] = {"value": steps * W * H * total_spp / e2e_s, "unit": "samples/s", "h2d_bytes_per_step": scene_bytes(desc.contents) * world,
+                          "d2h_bytes_per_step": W * H * 3 * 8, "ms_per_step": 1e3 * e2e_s / steps,
+                          "path": "rt_scene_create + rt_render(n_gpus=%d) with host buffers, every step" % world,
+                          "kernel_ms": float(np.mean([s["kernel_ms"] for s in stats])), "reduce_ms": float(np.mean([s["reduce_ms"] for s in stats])),
+                          "replicate_ms": float(np.mean([s["replicate_ms"] for s in stats])), "tail_ms": float(np.mean([s["tail_ms"] for s in stats])),
+                          "reduce_kind": stats[-1]["reduce_kind"], "gpus": stats[-1]["gpus"]}
+            if world > 1:
+                # strong scaling through the same call: the FIXED frame (spp total) split over the devices; scene kept resident
+                d2 = pkg.DeviceScene(desc, cx.local)
+                d2.render(W, H, spp, depth=50, seed=700, out=host_out, precision=prec, flags=flags, n_gpus=world)  # replicates
+                res = {}
+                for n in sorted({1, world}):
+                    sts = []
+                    d2.render(W, H, spp, depth=50, seed=701, out=host_out, precision=prec, flags=flags, n_gpus=n)
+                    t0 = time.perf_counter()
+                    for i in range(steps):
+                        sts.append(d2.render(W, H, spp, depth=50, seed=710 + i, out=host_out, precision=prec, flags=flags, n_gpus=n)[1])
+                    dt = time.perf_counter() - t0
+                    res[n] = {"value": steps * W * H * spp / dt, "ms_per_step": 1e3 * dt / steps, "kernel_ms": float(np.mean([s["kernel_ms"] for s in sts])),
+                              "reduce_ms": float(np.mean([s["reduce_ms"] for s in sts])), "tail_ms": float(np.mean([s["tail_ms"] for s in sts])),
+                              "d2h_ms": float(np.mean([s["d2h_ms"] for s in sts])), "gpu_kernel_ms": sts[-1]["gpu_kernel_ms"]}
+                t0 = time.perf_counter()
+                d3 = pkg.DeviceScene(desc, cx.local)
+                create_ms = 1e3 * (time.perf_counter() - t0)
+                d3.destroy()
+                out["strong"] = {"scaling": "strong", "frame": "%dx%d x %d spp split over %d GPUs inside one rt_render" % (W, H, spp, world),
+                                 "value": res[world]["value"], "unit": "samples/s", "one_gpu_value_same_call": res[1]["value"],
+                                 "efficiency": res[world]["value"] / (world * res[1]["value"]), "n": res[world], "one": res[1], "scene_create_ms": create_ms,
+                                 "limiter": "per step at N GPUs: kernel_ms (of which tail_ms is the persistent kernel's drain) + reduce_ms + d2h_ms + host overhead "
+                                            "(ms_per_step - the three)"}
+                # N-GPU frame == 1-GPU frame (small spp, outside every timed region)
+                a, _ = d2.render(W, H, 8, depth=50, seed=31, precision=prec, flags=flags, n_gpus=1)
+                b, _ = d2.render(W, H, 8, depth=50, seed=31, precision=prec, flags=flags, n_gpus=world)
+                okm = np.isfinite(a)
+                out["sharding_check"] = {"max_rel_diff": float(np.max(np.abs(a[okm] - b[okm]) / (np.abs(a[okm]) + 1e-3))) if okm.any() else 0.0,
+                                         "nan_masks_equal": bool(np.array_equal(np.isnan(a), np.isnan(b))), "spp": 8, "n_gpus": world, "bar": 1e-12}
+                d2.destroy()
+        cx.cpu_barrier()
+        if world > 1:
+            # the torch.distributed path's own check: sum of the ranks' shards vs rank 0's single-GPU render of the same small frame
+            chk = torch.zeros((H, W, 3), dtype=torch.float64, device=dev)
+            _dist.render_sharded(ds, W, H, 8, 50, 31, chk, stream=stream, precision=prec, flags=flags)
+            torch.cuda.synchronize()
+            if rank == 0:
+                a, _ = ds.render(W, H, 8, depth=50, seed=31, precision=prec, flags=flags, n_gpus=1)
+                b = chk.cpu().numpy()
+                okm = np.isfinite(a)
+                out["sharding_check"]["dist_max_rel_diff"] = float(np.max(np.abs(a[okm] - b[okm]) / (np.abs(a[okm]) + 1e-3))) if okm.any() else 0.0
+            cx.cpu_barrier()
+
+    if rank == 0 and cpu and world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        ref_spp = args.ref_spp or CPU_SPP[scene]
+        w, h, s, dt, _ = cpu_sample(scene, W, H, synth_n, ref_spp, 4242, cores)
+        out["cpu_baseline"] = {"value": w * h * s / dt, "unit": "samples/s", "cores": cores, "kind": "port",
+                               "sample": "%dx%d at %d spp, depth 50, oracle<double> in runRender's RNG plumbing, %d threads (%.1f s)" % (w, h, s, cores, dt)}
+    ds.destroy()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -145,12 +370,16 @@ def main():
     ap.add_argument("--spp", type=int, default=0)
     ap.add_argument("--ref-spp", type=int, default=0, help="spp of the CPU sample (default: 100 for the cpu_baseline leg = perflogs.org:1, 32 per step for --impl reference)")
     ap.add_argument("--synth-n", type=int, default=1000)
+    ap.add_argument("--size", default="", help="WxH override (synthetic)")
     ap.add_argument("--fast", action="store_true", help="RT_FLAG_FAST_MATH kernels (not bit-exact; reported separately)")
-    ap.add_argument("--precision", type=int, default=0)
+    ap.add_argument("--precision", type=int, default=1, help="0 fp32 (opt-in, biased on Book-1/2 scenes), 1 = RT_PREC_MIXED the production arithmetic, 2 fp64")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-per-scene", action="store_true", help="only the headline workload (profiling runs)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     W, H = SCENE_SIZE[args.scene]
+    if args.size:
+        W, H = (int(x) for x in args.size.split("x"))
     spp = args.spp or SCENE_SPP[args.scene]
     if args.impl == "reference":
         return run_reference(args, W, H, rank)
@@ -158,142 +387,66 @@ def main():
     import torch
     import torch.distributed as dist
     import rtb200_loader
-    pkg = rtb200_loader.load()
-    from ray_tracing_b200 import _dist
+    cx = Ctx()
+    cx.pkg = rtb200_loader.load(); cx.args = args; cx.rank, cx.world, cx.local = rank, world, local
     torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
+    cx.dev = torch.device("cuda", local)
+    gloo = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
-    flags = pkg.FLAG_FAST_MATH if args.fast else 0
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=cx.dev)
+        gloo = dist.new_group(backend="gloo")  # host-side barrier for the rank-0-only sections (an NCCL barrier would spin on the other GPUs)
 
-    hs = pkg.HostScene(args.scene, synth_n=args.synth_n)
-    desc = hs.desc(W, H)
-    ds = pkg.DeviceScene(desc, local)
-    fb = torch.zeros((H, W, 3), dtype=torch.float64, device=dev)
-    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
-    stream = torch.cuda.current_stream().cuda_stream
-    total_spp = spp * world  # weak scaling: every GPU renders `spp` samples per pixel
-
-    # algorithmic work per sample (instrumented kernel, small spp; the counters equal the oracle's, tests/test_gpu_parity.py)
-    work = None
-    if rank == 0:
-        _, st = ds.render(W, H, 2 if args.scene != "synthetic" else 1, counted=True, seed=99, precision=args.precision, flags=flags)
-        work = algorithmic_work(st["counters"])
-
-    def step(i):
-        flush_buf.zero_()  # L2 flush between iterations
-        fb.zero_()
-        s0, n = _dist.shard_samples(total_spp, rank, world)
-        ds.render_device(fb.data_ptr(), W, H, n, stream=stream, depth=50, seed=1 + i, s0=s0, precision=args.precision, flags=flags, total=total_spp)
-        _dist.reduce_framebuffer(fb, 0)
-
-    def sync():
-        if world > 1:
-            dist.barrier()
+    def cpu_barrier():
         torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier(group=gloo)
+    cx.cpu_barrier = cpu_barrier
+    cx.flush = torch.empty(256 << 20, dtype=torch.uint8, device=cx.dev)  # > 126 MB L2
+    cx.stream = torch.cuda.current_stream().cuda_stream
+    cx.peaks = _json("MEASURED_PEAKS.json")
+    cx.fp32 = _json("profiles/fp32_peak.json")
 
-    for i in range(args.warmup):
-        step(i)
-    sync()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    # kernel-only timing for the roofline: events right around the render kernel on its stream
-    k_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sync()
-    e0.record()
-    for i in range(args.steps):
-        flush_buf.zero_(); fb.zero_()
-        s0, n = _dist.shard_samples(total_spp, rank, world)
-        k_ev[i][0].record()
-        ds.render_device(fb.data_ptr(), W, H, n, stream=stream, depth=50, seed=100 + i, s0=s0, precision=args.precision, flags=flags, total=total_spp)
-        k_ev[i][1].record()
-        _dist.reduce_framebuffer(fb, 0)
-    e1.record()
-    sync()
-    ms = e0.elapsed_time(e1)
-    if world > 1:
-        t = torch.tensor([ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in k_ev]))
-    value = args.steps * W * H * total_spp / (ms / 1e3)
-    finite_frac = float(torch.isfinite(fb).all(dim=2).float().mean().item()) if rank == 0 else None
-
-    # ---- e2e: the user-facing calls with HOST buffers: rt_scene_create (H2D) + render + reduce + D2H of the frame, every step
-    host_out = np.zeros((H, W, 3))
-    pinned = torch.zeros((H, W, 3), dtype=torch.float64).pin_memory()
-
-    def e2e_step(i):
-        if world == 1:
-            tq = time.perf_counter()
-            d2 = pkg.DeviceScene(desc, local)
-            _, st = d2.render(W, H, spp, depth=50, seed=500 + i, out=host_out, precision=args.precision, flags=flags)
-            d2.destroy()
-            if os.environ.get("RTB_BENCH_DEBUG"):
-                print("e2e step %d: %.1f ms (kernel %.1f ms)" % (i, (time.perf_counter() - tq) * 1e3, st["kernel_ms"]), file=sys.stderr)
-        else:
-            d2 = pkg.DeviceScene(desc, local)
-            _dist.render_sharded(d2, W, H, total_spp, 50, 500 + i, fb, stream=stream, precision=args.precision, flags=flags)
-            if rank == 0:
-                pinned.copy_(fb, non_blocking=False)
-            d2.destroy()
-    e2e_step(0)
-    sync()
-    t0 = time.perf_counter()
-    for i in range(args.steps):
-        e2e_step(i)
-    sync()
-    e2e_s = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    e2e_value = args.steps * W * H * total_spp / e2e_s
-    # the sampler runs through both timed regions and is stopped only here: terminating nvidia-smi stalls the context for up to a
-    # few hundred ms, which the device-timed loop does not see but the wall-clocked end-to-end loop would
+    head = measure(cx, args.scene, spp, args.steps, args.warmup, synth_n=args.synth_n, size=(W, H))
+    # the sampler runs through both timed regions of the headline workload (terminating nvidia-smi stalls the context for up to a few
+    # hundred ms, which the wall-clocked end-to-end loop would see) and is stopped only here
     clocks = sampler.stop() if rank == 0 else None
 
+    per_scene = {}
+    if not args.no_per_scene and args.scene == "random" and not args.fast:
+        small = max(2, min(args.steps, 3))
+        if world == 1:
+            plan = [("cfg1", "random_book1", 1024, small, 2, 1000, None), ("cfg3", "next_week_final", 256, 2, 1, 1000, None),
+                    ("cfg4", "cornell", 1000, small, 2, 1000, None), ("cfg5_90k", "synthetic", 1, 2, 1, 300, (480, 270)),
+                    ("cfg5_1m", "synthetic", 1, 1, 1, 1000, (240, 135))]
+        else:
+            plan = [("cfg3", "next_week_final", 256, 2, 1, 1000, None), ("cfg4", "cornell", 1000, 2, 1, 1000, None)]
+        for key, sc, s, st, wu, sn, size in plan:
+            r = measure(cx, sc, s, st, wu, synth_n=sn, size=size)
+            if rank == 0:
+                per_scene[key] = r
+
     if rank == 0:
-        pk = peaks()
-        hbm_peak = pk["hbm_gbs"] if pk else 6650.0
-        bytes_ps, flops_ps, per_sample = work
-        samples_per_launch = W * H * spp
-        ach_gbs = bytes_ps * samples_per_launch / (kernel_ms / 1e3) / 1e9
-        ach_tf = flops_ps * samples_per_launch / (kernel_ms / 1e3) / 1e12
+        e2e = head.pop("e2e")
         line = {
-            "metric": "samples/sec", "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": ["f32", "f32+f64 sphere", "f64"][args.precision], "data": "synthetic",
-            "config": {"workload": SCENE_DOC[args.scene], "scene": args.scene, "width": W, "height": H, "spp_per_gpu_per_step": spp, "max_depth": 50,
-                       "seed": "randGen 1024", "lights": "HEAD", "parallelism": "spp-sharded x%d + ncclReduce" % world, "l2": "flushed between steps (256 MiB write)",
-                       "arithmetic": "fast-math" if args.fast else "literal (no FMA contraction, IEEE div/sqrt)", "finite_pixel_fraction": finite_frac},
-            "roofline": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak, "traffic": measured_traffic(args.scene, W, H, spp),
-                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst)" if pk else "fallback 6.65 TB/s", "kernel": "renderKernel", "kernel_ms": kernel_ms,
-                         "algorithmic_bytes_per_sample": bytes_ps, "per_sample": per_sample,
-                         "note": "scene is L1/L2-resident (KBs..MBs); the binding roofline is FP32 issue under divergence, see roofline_fp32"},
-            "roofline_fp32": {"bound": "fp32-issue", "achieved": ach_tf, "peak": FP32_PEAK_TFLOPS_NOMINAL, "unit": "TFLOP/s", "frac": ach_tf / FP32_PEAK_TFLOPS_NOMINAL,
-                              "peak_source": "nominal 148 SM x 128 lanes x 2 x 1.965 GHz", "algorithmic_flops_per_sample": flops_ps},
-            "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": scene_bytes(desc.contents), "d2h_bytes_per_step": W * H * 3 * 8},
-            "gpu_launches": args.steps, "clocks": clocks,
+            "metric": "samples/sec", "value": head["value"], "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": ["f32", "f32 + f64 sphere quadratic (RT_PREC_MIXED, the production arithmetic)", "f64"][args.precision], "data": "synthetic",
+            "config": {"workload": head["workload"], "scene": args.scene, "width": W, "height": H, "spp_per_gpu_per_step": spp, "max_depth": 50,
+                       "seed": "randGen 1024", "lights": "HEAD", "parallelism": "spp-sharded x%d + ncclReduce (torch.distributed)" % world,
+                       "l2": "flushed between steps (256 MiB write)",
+                       "arithmetic": "fast-math" if args.fast else "literal (no FMA contraction, IEEE div/sqrt)", "finite_pixel_fraction": head["finite_pixel_fraction"]},
+            "roofline": head["roofline"], "e2e": e2e, "gpu_launches": args.steps, "clocks": clocks,
         }
-        if world == 1 and not args.no_cpu_baseline:
-            sys.path.insert(0, os.path.join(ROOT, "oracle"))
-            import oracle as O
-            earth = pkg.load_earth() if args.scene in ("earth", "random", "next_week_final") else None
-            osc = O.OracleScene(args.scene, earth=earth, synth_n=args.synth_n)
-            cores = os.cpu_count() or 1
-            w, h = (W, H) if args.scene != "synthetic" else (48, 27)
-            ref_spp = 1 if args.scene == "synthetic" else (args.ref_spp or {"random": 100, "random_book1": 100, "cornell": 100, "next_week_final": 16}[args.scene])
-            t0 = time.time()
-            osc.render(w, h, ref_spp, depth=50, prec=O.PREC_F64, mode=0, seed=4242, threads=cores)
-            dt = time.time() - t0
-            line["cpu_baseline"] = {"value": w * h * ref_spp / dt, "unit": "samples/s", "cores": cores, "kind": "port",
-                                    "sample": "%dx%d at %d spp, depth 50, oracle<double> in runRender's RNG plumbing, %d threads (%.1f s)" % (w, h, ref_spp, cores, dt)}
+        for k in ("cpu_baseline", "strong", "sharding_check"):
+            if k in head:
+                line[k] = head[k]
+        if per_scene:
+            line["per_scene"] = per_scene
         print(json.dumps(line))
-    ds.destroy()
     if world > 1:
         dist.destroy_process_group()
 

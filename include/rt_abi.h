@@ -153,6 +153,12 @@ enum RtPrecision {
                                   (ray-tracing_b200/csrc/rt_strict_math.h) instead of libdevice, so that a path is bit-identical to the
                                   test oracle's; same kernels, same step and draw order.  Excludes RT_FLAG_FAST_MATH. */
 
+#define RT_FLAG_COOP 4u        /* force the warp-cooperative scan-stream traversal (one path per warp; ray-tracing_b200/csrc/rt_coop.cuh);
+                                  RT_ERR_UNSUPPORTED when the scene is not eligible (world = a BVH of spheres / rects only, light list =
+                                  one primitive or Unhittable).  Default: chosen automatically for eligible scenes with a large BVH,
+                                  where per-path latency, not throughput, bounds a frame (cfg5).  Same visits, same order, same image. */
+#define RT_FLAG_NO_COOP 8u     /* never use it */
+
 typedef struct RtRenderParams {
   uint32_t width, height;     /* full image size (imageWidth, imageHeight of mkRenderStaticEnv, Lib.hs:92-108) */
   uint32_t sample_offset;     /* first sample index rendered by this call */
@@ -185,6 +191,8 @@ typedef struct RtStats {
   uint32_t gpus;           /* devices that rendered a share of this call (1 for single-device calls) */
   uint32_t reduce_kind;    /* RT_REDUCE_* actually used */
   double gpu_kernel_ms[16];/* per device share: kernel time (kernel_ms is their maximum) */
+  uint32_t kernel_kind;    /* 0 = renderKernel (one path per lane), 1 = renderKernelCoop (one path per warp, scan stream) */
+  uint32_t reserved0;
   double tail_ms;          /* the persistent kernel's drain: from the first warp that found the path index space empty to the exit of
                               the last warp (device globaltimer; the maximum over the devices of a multi-GPU call) */
 } RtStats;

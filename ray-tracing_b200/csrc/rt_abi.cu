@@ -46,6 +46,10 @@ struct HostScene {
   std::vector<uint32_t> node_lsize, node_rsize;  // htblSize of the children (Lib.hs:662-671)
   int stackDepth = 1;
   uint32_t lightCap = 0;  // entries of the light-pdf walk stack (rt_traverse.cuh)
+  // scan stream of the warp-cooperative traversal (rt_coop.cuh): eligible when the world is a BVH whose leaves are spheres / rects /
+  // Unhittable only and the light list is one primitive or Unhittable; coopRecords = records of the pre-order expansion
+  bool coopEligible = false;
+  uint64_t coopRecords = 0;
 };
 
 template <class T> struct DevBuffers {
@@ -246,8 +250,38 @@ template <class T> int buildDevice(const HostScene& h, DevBuffers<T>& db) {
   for (size_t i = 0; i < (size_t)h.n_perlin * 256; ++i) pvec[i] = Q{(T)h.perlin_ranvec[i * 3], (T)h.perlin_ranvec[i * 3 + 1], (T)h.perlin_ranvec[i * 3 + 2], (T)0};
   for (size_t i = 0; i < (size_t)h.n_perlin * 768; ++i) pperm[i] = (uint8_t)(h.perlin_perm[i] & 255);
 
+  // scan stream (rt_coop.cuh): the world BVH in reference visit order — a node, its whole left subtree, its right subtree
+  // (Lib.hs:971-988) — every node carrying the index of the first record behind its subtree
+  std::vector<Q> coop;
+  if (h.coopEligible) {
+    coop.reserve(2 * (size_t)h.coopRecords);
+    std::function<void(uint32_t)> emit = [&](uint32_t ref) {
+      const uint32_t k = ref >> 28, i = ref & kIdxMask;
+      const size_t at = coop.size();
+      if (k == K_BVH) {
+        const double* b = &h.node_box[(size_t)i * 6];
+        coop.push_back(Q{(T)b[0], (T)b[1], (T)b[2], B(0u)});
+        coop.push_back(Q{(T)b[3], (T)b[4], (T)b[5], B(ref)});
+        emit(h.node_left[i]); emit(h.node_right[i]);
+        coop[at].w = B((uint32_t)(coop.size() / 2));
+      } else if (k == K_SPHERE) {
+        const double* sp = &h.sphere_cr[(size_t)i * 4];
+        coop.push_back(Q{(T)sp[0], (T)sp[1], (T)sp[2], (T)sp[3]});
+        coop.push_back(Q{(T)0, (T)0, (T)0, B(ref)});
+      } else if (k >= K_RECT_XY && k <= K_RECT_YZ) {
+        const double* r = &h.rect[(size_t)i * 5];
+        coop.push_back(Q{(T)r[0], (T)r[1], (T)r[2], (T)r[3]});
+        coop.push_back(Q{(T)r[4], (T)0, (T)0, B(ref)});
+      } else {  // Unhittable
+        coop.push_back(Q{(T)0, (T)0, (T)0, (T)0});
+        coop.push_back(Q{(T)0, (T)0, (T)0, B(ref)});
+      }
+    };
+    emit(h.world_root);
+  }
   DScene<T>& sc = db.sc;
   BlobLayout L;
+  const size_t oCoop = L.add(coop);
   const size_t oNodes = L.add(nodes), oNsz = L.add(nsz), oSph = L.add(spheres), oSmat = L.add(h.sphere_mat), oMov = L.add(moving), oRect = L.add(rects),
                oCub = L.add(cuboids), oTr = L.add(translates), oRot = L.add(rotates), oMed = L.add(media), oMat = L.add(mats), oTex = L.add(texs),
                oPv = L.add(pvec), oPp = L.add(pperm);
@@ -286,6 +320,7 @@ template <class T> int buildDevice(const HostScene& h, DevBuffers<T>& db) {
   sc.mats = static_cast<const Q*>(at(oMat, mats.size())); sc.texs = static_cast<const Q*>(at(oTex, texs.size()));
   sc.perlin_vec = static_cast<const Q*>(at(oPv, pvec.size())); sc.perlin_perm = static_cast<const uint8_t*>(at(oPp, pperm.size()));
   sc.images = static_cast<const DImage*>(at(oImgTab, imgs.size()));
+  sc.coop = static_cast<const Q*>(at(oCoop, coop.size())); sc.coop_n = (uint32_t)(coop.size() / 2); sc.pad2_ = 0;
   sc.world_root = h.world_root; sc.lights_root = h.lights_root;
   sc.bigCoords = 0; sc.pad_ = 0;
   for (double v : h.node_box) if (!(std::fabs(v) <= 1099511627776.0)) sc.bigCoords = 1;  // beyond 2^40 or non-finite (rt_device.cuh kDivHi)
@@ -340,7 +375,18 @@ uint32_t tuneParam(const char* name, uint32_t dflt) {
 struct PathLog { uint32_t* prim = nullptr; double* t = nullptr; uint32_t stride = 0; };
 
 // launches the render kernel of one device into d_out (accumulating).  instr: 0 production, 1 counters, 3 path log
-int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, double* d_out, cudaStream_t st, int instr, int* gridOut, const PathLog* plog = nullptr) {
+// scan-stream traversal: forced by RT_FLAG_COOP, forbidden by RT_FLAG_NO_COOP / fast math, otherwise chosen for eligible scenes whose
+// BVH is large enough that one path is a long dependent chain (RTB_COOP_MIN_NODES, default 32768 nodes)
+bool useCoop(const HostScene& hs, uint32_t flags) {
+  if (!hs.coopEligible || (flags & (RT_FLAG_NO_COOP | RT_FLAG_FAST_MATH))) return false;
+  if (flags & RT_FLAG_COOP) return true;
+  return hs.n_nodes >= tuneParam("RTB_COOP_MIN_NODES", 32768);
+}
+
+int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, double* d_out, cudaStream_t st, int instr, int* gridOut, const PathLog* plog = nullptr,
+                 uint32_t* kindOut = nullptr) {
+  if ((q.flags & RT_FLAG_COOP) && !hs.coopEligible)
+    return fail(RT_ERR_UNSUPPORTED, "RT_FLAG_COOP: the scene is not eligible for the scan-stream traversal (world must be a BVH of spheres / rects, light list one primitive)");
   const void* dsc = nullptr;
   int rc = deviceScene(hs, c, q.precision, &dsc);
   if (rc) return rc;
@@ -370,8 +416,12 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
   a.lightCap = hs.lightCap;
   a.counter = c->d_counter; a.ctr = instr == 1 ? c->d_counter + kCtrWorkBase : nullptr; a.out = d_out;
   if (plog) { a.plogPrim = plog->prim; a.plogT = plog->t; a.plogStride = plog->stride; }
+  const bool coop = useCoop(hs, q.flags);
+  if (kindOut) *kindOut = coop ? 1u : 0u;
   cudaError_t ce;
-  if (q.flags & RT_FLAG_FAST_MATH) ce = launchRender<MATH_FAST>((int)q.precision, instr == 3 ? 0 : instr, dsc, a, hs.stackDepth, c->numSMs, st, gridOut);
+  if (coop && (q.flags & RT_FLAG_STRICT_MATH)) ce = launchRenderCoop<MATH_STRICT>((int)q.precision, instr, dsc, a, c->numSMs, st, gridOut);
+  else if (coop) ce = launchRenderCoop<MATH_LITERAL>((int)q.precision, instr, dsc, a, c->numSMs, st, gridOut);
+  else if (q.flags & RT_FLAG_FAST_MATH) ce = launchRender<MATH_FAST>((int)q.precision, instr == 3 ? 0 : instr, dsc, a, hs.stackDepth, c->numSMs, st, gridOut);
   else if (q.flags & RT_FLAG_STRICT_MATH) ce = launchRender<MATH_STRICT>((int)q.precision, instr, dsc, a, hs.stackDepth, c->numSMs, st, gridOut);
   else ce = launchRender<MATH_LITERAL>((int)q.precision, instr, dsc, a, hs.stackDepth, c->numSMs, st, gridOut);
   if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("render launch: ") + cudaGetErrorString(ce));
@@ -458,6 +508,7 @@ int renderMulti(SceneEntry* e, const RtRenderParams& q, int nGpus, double* out, 
     allPeer = allPeer && can;
   }
   // shares
+  uint32_t kernelKind = 0;
   const bool bySamples = q.sample_count >= (uint32_t)n;
   const uint32_t rows = q.row1 - q.row0;
   for (int k = 0; k < n; ++k) {
@@ -475,7 +526,7 @@ int renderMulti(SceneEntry* e, const RtRenderParams& q, int nGpus, double* out, 
     CU(cudaSetDevice(devs[k]));
     CU(cudaMemsetAsync(ctx[k]->d_fb, 0, elems * sizeof(double), ctx[k]->stream));
     CU(cudaEventRecord(ctx[k]->evStart, ctx[k]->stream));
-    if ((rc = renderLaunch(e->hs, ctx[k], qk, ctx[k]->d_fb, ctx[k]->stream, 0, nullptr))) return rc;
+    if ((rc = renderLaunch(e->hs, ctx[k], qk, ctx[k]->d_fb, ctx[k]->stream, 0, nullptr, nullptr, &kernelKind))) return rc;
     CU(cudaEventRecord(ctx[k]->evDone, ctx[k]->stream));
   }
   // reduction onto the root
@@ -551,7 +602,7 @@ int renderMulti(SceneEntry* e, const RtRenderParams& q, int nGpus, double* out, 
     cudaEventElapsedTime(&ms, evs.ev[1], evs.ev[2]); stats->d2h_ms = ms;
     stats->samples = (uint64_t)(q.row1 - q.row0) * (q.col1 - q.col0) * q.sample_count;
     stats->launches = (uint64_t)n + (kind == RT_REDUCE_PEER ? 1 : 0);
-    stats->gpus = (uint32_t)n; stats->reduce_kind = kind; stats->replicate_ms = replicateMs;
+    stats->gpus = (uint32_t)n; stats->reduce_kind = kind; stats->replicate_ms = replicateMs; stats->kernel_kind = kernelKind;
   }
   return RT_OK;
 }
@@ -594,7 +645,8 @@ int renderHost(rt_scene_t scene, const RtRenderParams* params, double* out, RtSt
   CU(cudaMemsetAsync(c->d_fb, 0, elems * sizeof(double), 0));
   CU(cudaEventRecord(e0, 0));
   int grid = 0;
-  rc = renderLaunch(e->hs, c, q, c->d_fb, 0, instr, &grid, instr == 3 ? &dlog : nullptr);
+  uint32_t kernelKind = 0;
+  rc = renderLaunch(e->hs, c, q, c->d_fb, 0, instr, &grid, instr == 3 ? &dlog : nullptr, &kernelKind);
   if (rc) return rc;
   CU(cudaEventRecord(e1, 0));
   // copy back only the rows of the region
@@ -615,7 +667,7 @@ int renderHost(rt_scene_t scene, const RtRenderParams* params, double* out, RtSt
     cudaEventElapsedTime(&ms, e1, e2); stats->d2h_ms = ms;
     stats->samples = (uint64_t)paths;
     stats->launches = q.sample_count ? 1 : 0;
-    stats->gpus = 1;
+    stats->gpus = 1; stats->kernel_kind = kernelKind;
     unsigned long long cc[kCtrTotal];
     CU(cudaMemcpy(cc, c->d_counter, sizeof(cc), cudaMemcpyDeviceToHost));
     if (instr == 1) {
@@ -785,6 +837,26 @@ int rt_scene_create(const RtSceneDesc* d, int device, rt_scene_t* out) {
   if (frames > kMaxFrames) return fail(RT_ERR_UNSUPPORTED, "more than " + std::to_string(kMaxFrames) + " nested Translate/Rotate frames");
   if (media > 1) return fail(RT_ERR_UNSUPPORTED, "ConstantMedium nested inside a ConstantMedium boundary");
   if (lightDepth(h, h.lights_root) + 1 > kMaxLightDepth) return fail(RT_ERR_UNSUPPORTED, "lights BVH too deep");
+  {  // scan-stream eligibility and size (memoised expansion count; shared subtrees are expanded once per reference)
+    std::map<uint32_t, uint64_t> count;
+    bool ok = (h.world_root >> 28) == K_BVH;
+    std::function<uint64_t(uint32_t)> expand = [&](uint32_t ref) -> uint64_t {
+      const uint32_t k = ref >> 28;
+      if (k == K_SPHERE || (k >= K_RECT_XY && k <= K_RECT_YZ) || k == K_UNHITTABLE) return 1;
+      if (k != K_BVH) { ok = false; return 1; }
+      auto it = count.find(ref);
+      if (it != count.end()) return it->second;
+      const uint32_t i = ref & kIdxMask;
+      const uint64_t c = 1 + expand(h.node_left[i]) + expand(h.node_right[i]);
+      count[ref] = c;
+      return c;
+    };
+    const uint64_t total = ok ? expand(h.world_root) : 0;
+    const uint32_t lk = h.lights_root >> 28;
+    ok = ok && (lk == K_UNHITTABLE || lk == K_SPHERE || (lk >= K_RECT_XY && lk <= K_RECT_YZ));
+    ok = ok && total <= 4ull * ((uint64_t)h.n_nodes + h.n_spheres + h.n_rects) + 16 && total < (1ull << 30);
+    h.coopEligible = ok; h.coopRecords = ok ? total : 0;
+  }
   h.stackDepth = stackNeed;
   h.lightCap = (h.lights_root >> 28) == K_BVH ? (uint32_t)lightDepth(h, h.lights_root) : 0u;  // DFS over L levels holds at most L entries
   h.node_lsize.resize(h.n_nodes); h.node_rsize.resize(h.n_nodes);
@@ -850,7 +922,8 @@ int rt_render_device(rt_scene_t scene, const RtRenderParams* params, double* d_o
   Events evs;
   if (stats) { CU(evs.create(2)); CU(cudaEventRecord(evs.ev[0], st)); }
   const cudaEvent_t e0 = evs.ev[0], e1 = evs.ev[1];
-  rc = renderLaunch(e->hs, &e->main, q, d_out, st, 0, nullptr);
+  uint32_t kernelKind = 0;
+  rc = renderLaunch(e->hs, &e->main, q, d_out, st, 0, nullptr, nullptr, &kernelKind);
   if (rc) return rc;
   if (stats) {
     CU(cudaEventRecord(e1, st));
@@ -858,7 +931,7 @@ int rt_render_device(rt_scene_t scene, const RtRenderParams* params, double* d_o
     std::memset(stats, 0, sizeof(*stats));
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
     stats->kernel_ms = ms; stats->samples = (uint64_t)(q.row1 - q.row0) * (q.col1 - q.col0) * q.sample_count; stats->launches = q.sample_count ? 1 : 0;
-    stats->gpus = 1; stats->gpu_kernel_ms[0] = ms;
+    stats->gpus = 1; stats->gpu_kernel_ms[0] = ms; stats->kernel_kind = kernelKind;
   }
   return RT_OK;
 }
@@ -888,7 +961,10 @@ int rt_trace(rt_scene_t scene, uint32_t precision, uint32_t flags, uint32_t n, c
   a.n = n; a.logStride = log_stride; a.tmin = t_min; a.tmax = t_max; a.seed = seed; a.rays = (const double*)bRays.p;
   a.hit = (int32_t*)bHit.p; a.rec = (double*)bRec.p; a.prim = (uint32_t*)bPrim.p; a.mat = (uint32_t*)bMat.p; a.front = (uint8_t*)bFront.p;
   a.nvisit = (unsigned long long*)bNv.p; a.vhash = (unsigned long long*)bVh.p; a.vlog = (uint32_t*)bLog.p;
-  cudaError_t ce = (flags & RT_FLAG_FAST_MATH) ? launchTrace<MATH_FAST>((int)precision, dsc, a, e->hs.stackDepth, 0)
+  if ((flags & RT_FLAG_COOP) && !e->hs.coopEligible) return fail(RT_ERR_UNSUPPORTED, "RT_FLAG_COOP: the scene is not eligible for the scan-stream traversal");
+  const bool coop = useCoop(e->hs, flags);
+  cudaError_t ce = coop ? ((flags & RT_FLAG_STRICT_MATH) ? launchTraceCoop<MATH_STRICT>((int)precision, dsc, a, 0) : launchTraceCoop<MATH_LITERAL>((int)precision, dsc, a, 0))
+                   : (flags & RT_FLAG_FAST_MATH) ? launchTrace<MATH_FAST>((int)precision, dsc, a, e->hs.stackDepth, 0)
                    : (flags & RT_FLAG_STRICT_MATH) ? launchTrace<MATH_STRICT>((int)precision, dsc, a, e->hs.stackDepth, 0)
                                                    : launchTrace<MATH_LITERAL>((int)precision, dsc, a, e->hs.stackDepth, 0);
   if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("trace launch: ") + cudaGetErrorString(ce));

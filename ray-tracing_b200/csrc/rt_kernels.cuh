@@ -25,6 +25,9 @@ template <class T> struct MinBlocks { static constexpr int v = RTB_MIN_BLOCKS; }
 template <> struct MinBlocks<double> { static constexpr int v = 1; };
 
 #include "rt_render_kernel.inl"
+}  // namespace rtb
+#include "rt_coop.cuh"
+namespace rtb {
 
 template <class T, int MODE>
 __global__ void textureKernel(const __grid_constant__ DScene<T> sc, uint32_t tex, uint32_t n, const double* q, double* out) {
@@ -83,6 +86,48 @@ cudaError_t launchTrace(int prec, const void* dscene, const TraceArgs& a, int st
   if (prec == 0) return launchTraceT<float, float, MODE>(*static_cast<const DScene<float>*>(dscene), a, stackDepth, st);
   if (prec == 1) return launchTraceT<float, double, MODE>(*static_cast<const DScene<float>*>(dscene), a, stackDepth, st);
   return launchTraceT<double, double, MODE>(*static_cast<const DScene<double>*>(dscene), a, stackDepth, st);
+}
+
+// ---- scan-stream (warp-cooperative) kernels: persistent warps, no shared memory
+template <class T, class S, int INSTR, int MODE>
+static cudaError_t launchRenderCoopT(const DScene<T>& sc, const RenderArgs& a, int numSMs, cudaStream_t st, int* gridOut) {
+  auto kern = renderKernelCoop<T, S, INSTR, MODE>;
+  int perSM = 0;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, kern, kBlock, 0);
+  if (e != cudaSuccess) return e;
+  if (perSM < 1) perSM = 1;
+  if (const char* v = std::getenv("RTB_COOP_BLOCKS_PER_SM")) perSM = std::max(1, std::min(perSM, std::atoi(v)));  // tuning experiments only
+  // one resident wave, but never more warps than paths (a warp owns a whole path)
+  const unsigned long long warpsWanted = a.total_paths;
+  int grid = (int)std::min<unsigned long long>((unsigned long long)numSMs * perSM, (warpsWanted + (kBlock / 32) - 1) / (kBlock / 32));
+  if (grid < 1) grid = 1;
+  if (gridOut) *gridOut = grid;
+  kern<<<grid, kBlock, 0, st>>>(sc, a);
+  return cudaGetLastError();
+}
+template <class T, class S, int MODE>
+static cudaError_t launchRenderCoopI(int instr, const DScene<T>& sc, const RenderArgs& a, int numSMs, cudaStream_t st, int* gridOut) {
+  if (instr == 1) return launchRenderCoopT<T, S, 1, MODE>(sc, a, numSMs, st, gridOut);
+  if (instr == 3) return launchRenderCoopT<T, S, 3, MODE>(sc, a, numSMs, st, gridOut);
+  return launchRenderCoopT<T, S, 0, MODE>(sc, a, numSMs, st, gridOut);
+}
+template <int MODE>
+cudaError_t launchRenderCoop(int prec, int instr, const void* dscene, const RenderArgs& a, int numSMs, cudaStream_t st, int* gridOut) {
+  if (prec == 0) return launchRenderCoopI<float, float, MODE>(instr, *static_cast<const DScene<float>*>(dscene), a, numSMs, st, gridOut);
+  if (prec == 1) return launchRenderCoopI<float, double, MODE>(instr, *static_cast<const DScene<float>*>(dscene), a, numSMs, st, gridOut);
+  return launchRenderCoopI<double, double, MODE>(instr, *static_cast<const DScene<double>*>(dscene), a, numSMs, st, gridOut);
+}
+template <class T, class S, int MODE>
+static cudaError_t launchTraceCoopT(const DScene<T>& sc, const TraceArgs& a, cudaStream_t st) {
+  const unsigned long long threads = (unsigned long long)a.n * 32ull;
+  traceKernelCoop<T, S, MODE><<<(unsigned)((threads + kBlock - 1) / kBlock), kBlock, 0, st>>>(sc, a);
+  return cudaGetLastError();
+}
+template <int MODE>
+cudaError_t launchTraceCoop(int prec, const void* dscene, const TraceArgs& a, cudaStream_t st) {
+  if (prec == 0) return launchTraceCoopT<float, float, MODE>(*static_cast<const DScene<float>*>(dscene), a, st);
+  if (prec == 1) return launchTraceCoopT<float, double, MODE>(*static_cast<const DScene<float>*>(dscene), a, st);
+  return launchTraceCoopT<double, double, MODE>(*static_cast<const DScene<double>*>(dscene), a, st);
 }
 
 template <int MODE>

@@ -37,6 +37,9 @@ struct TraceArgs {
 // MODE: 0 literal arithmetic (rt_launch_exact.cu), 1 fast math (rt_launch_fast.cu), 2 strict math (rt_launch_strict.cu); instr: 0, 1 (counters), 3 (path log)
 template <int MODE> cudaError_t launchRender(int prec, int instr, const void* dscene, const RenderArgs& a, int stackDepth, int numSMs, cudaStream_t st, int* gridOut);
 template <int MODE> cudaError_t launchTrace(int prec, const void* dscene, const TraceArgs& a, int stackDepth, cudaStream_t st);
+// scan-stream (warp-cooperative, rt_coop.cuh) variants for eligible scenes; MODE 0 and 2 only
+template <int MODE> cudaError_t launchRenderCoop(int prec, int instr, const void* dscene, const RenderArgs& a, int numSMs, cudaStream_t st, int* gridOut);
+template <int MODE> cudaError_t launchTraceCoop(int prec, const void* dscene, const TraceArgs& a, cudaStream_t st);
 template <int MODE> cudaError_t launchTexture(int prec, const void* dscene, uint32_t tex, uint32_t n, const double* q, double* out, cudaStream_t st);
 cudaError_t launchStrictMathEval(uint32_t fn, uint32_t n, const double* x, const double* y, double* out, int as_float, cudaStream_t st);
 cudaError_t launchDivSelftest(unsigned long long n, unsigned long long seed, unsigned long long* out2, cudaStream_t st);

@@ -40,6 +40,8 @@ cudaError_t launchDivSelftest(unsigned long long n, unsigned long long seed, uns
 
 template cudaError_t launchRender<MATH_LITERAL>(int, int, const void*, const RenderArgs&, int, int, cudaStream_t, int*);
 template cudaError_t launchTrace<MATH_LITERAL>(int, const void*, const TraceArgs&, int, cudaStream_t);
+template cudaError_t launchRenderCoop<MATH_LITERAL>(int, int, const void*, const RenderArgs&, int, cudaStream_t, int*);
+template cudaError_t launchTraceCoop<MATH_LITERAL>(int, const void*, const TraceArgs&, cudaStream_t);
 template cudaError_t launchTexture<MATH_LITERAL>(int, const void*, uint32_t, uint32_t, const double*, double*, cudaStream_t);
 
 cudaError_t launchTonemap(const double* sum, uint32_t n, double ns, uint8_t* out, cudaStream_t st) {

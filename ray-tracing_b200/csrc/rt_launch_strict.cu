@@ -7,6 +7,8 @@
 namespace rtb {
 template cudaError_t launchRender<MATH_STRICT>(int, int, const void*, const RenderArgs&, int, int, cudaStream_t, int*);
 template cudaError_t launchTrace<MATH_STRICT>(int, const void*, const TraceArgs&, int, cudaStream_t);
+template cudaError_t launchRenderCoop<MATH_STRICT>(int, int, const void*, const RenderArgs&, int, cudaStream_t, int*);
+template cudaError_t launchTraceCoop<MATH_STRICT>(int, const void*, const TraceArgs&, cudaStream_t);
 template cudaError_t launchTexture<MATH_STRICT>(int, const void*, uint32_t, uint32_t, const double*, double*, cudaStream_t);
 
 // device evaluation of the shared functions for the host/device identity test (tests/test_gpu_strict.py)

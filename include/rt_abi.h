@@ -158,6 +158,10 @@ enum RtPrecision {
                                   one primitive or Unhittable).  Default: chosen automatically for eligible scenes with a large BVH,
                                   where per-path latency, not throughput, bounds a frame (cfg5).  Same visits, same order, same image. */
 #define RT_FLAG_NO_COOP 8u     /* never use it */
+#define RT_FLAG_WAVEFRONT 16u  /* force the split traversal / shade kernels over path-state slots in HBM (rt_wavefront.cuh; fp32 / mixed,
+                                  literal math; otherwise RT_ERR_UNSUPPORTED).  Default: chosen per scene (shading-heavy scenes).  Same
+                                  steps, draws and arithmetic per path as renderKernel: the same image. */
+#define RT_FLAG_NO_WAVEFRONT 32u /* never use it */
 
 typedef struct RtRenderParams {
   uint32_t width, height;     /* full image size (imageWidth, imageHeight of mkRenderStaticEnv, Lib.hs:92-108) */
@@ -191,8 +195,8 @@ typedef struct RtStats {
   uint32_t gpus;           /* devices that rendered a share of this call (1 for single-device calls) */
   uint32_t reduce_kind;    /* RT_REDUCE_* actually used */
   double gpu_kernel_ms[16];/* per device share: kernel time (kernel_ms is their maximum) */
-  uint32_t kernel_kind;    /* 0 = renderKernel (one path per lane), 1 = renderKernelCoop (one path per warp, scan stream) */
-  uint32_t reserved0;
+  uint32_t kernel_kind;    /* 0 = renderKernel (one path per lane), 1 = renderKernelCoop (one path per warp, scan stream), 2 = wavefront (wfTraverse + wfShade rounds) */
+  uint32_t rounds;         /* wavefront: rounds of (shade, traverse) launched */
   double tail_ms;          /* the persistent kernel's drain: from the first warp that found the path index space empty to the exit of
                               the last warp (device globaltimer; the maximum over the devices of a multi-GPU call) */
 } RtStats;

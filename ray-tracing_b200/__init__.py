@@ -21,6 +21,8 @@ FLAG_FAST_MATH = 1
 FLAG_STRICT_MATH = 2
 FLAG_COOP = 4
 FLAG_NO_COOP = 8
+FLAG_WAVEFRONT = 16
+FLAG_NO_WAVEFRONT = 32
 INIT_NCCL = 1
 REDUCE_KINDS = ["none", "peer-kernel", "nccl", "staged"]
 RT_NONE = 0xFFFFFFFF
@@ -65,7 +67,7 @@ class RtStats(C.Structure):
     _fields_ = [("kernel_ms", C.c_double), ("h2d_ms", C.c_double), ("d2h_ms", C.c_double), ("samples", C.c_uint64),
                 ("launches", C.c_uint64), ("counters", C.c_uint64 * 24), ("sched", C.c_uint64 * 16),
                 ("reduce_ms", C.c_double), ("replicate_ms", C.c_double), ("gpus", C.c_uint32), ("reduce_kind", C.c_uint32),
-                ("gpu_kernel_ms", C.c_double * 16), ("kernel_kind", C.c_uint32), ("reserved0", C.c_uint32), ("tail_ms", C.c_double)]
+                ("gpu_kernel_ms", C.c_double * 16), ("kernel_kind", C.c_uint32), ("rounds", C.c_uint32), ("tail_ms", C.c_double)]
 
 
 class RtLimits(C.Structure):

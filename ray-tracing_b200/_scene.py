@@ -115,7 +115,7 @@ class DeviceScene:
         fn = core().rt_render_counted if counted else core().rt_render
         _check(fn(self.id, C.byref(p), _p(out), C.byref(st)))
         stats = dict(kernel_ms=st.kernel_ms, d2h_ms=st.d2h_ms, samples=int(st.samples), launches=int(st.launches), gpus=int(st.gpus),
-                     reduce_ms=st.reduce_ms, replicate_ms=st.replicate_ms, tail_ms=st.tail_ms, kernel=["renderKernel", "renderKernelCoop"][st.kernel_kind], reduce_kind=REDUCE_KINDS[st.reduce_kind],
+                     reduce_ms=st.reduce_ms, replicate_ms=st.replicate_ms, tail_ms=st.tail_ms, kernel=["renderKernel", "renderKernelCoop", "wavefront"][st.kernel_kind], rounds=int(st.rounds), reduce_kind=REDUCE_KINDS[st.reduce_kind],
                      gpu_kernel_ms=[float(x) for x in st.gpu_kernel_ms[:max(int(st.gpus), 1)]])
         if counted:
             stats["counters"] = dict(zip(COUNTER_NAMES, (int(x) for x in st.counters)))

@@ -4,6 +4,7 @@
 // compute entry point returns RT_ERR_CUDA.
 #include "../../include/rt_abi.h"
 #include "rt_device.cuh"
+#include "rt_traverse.cuh"  // kBlock, column layout
 #include "rt_launch.h"
 
 #include <dlfcn.h>
@@ -66,11 +67,17 @@ struct DeviceCtx {
   DevBuffers<double> f64;
   unsigned long long* d_counter = nullptr;  // kCtrTotal words: [0] path counter, work counters, scheduler statistics, tail stamps (rt_device.cuh kCtr*)
   double* d_fb = nullptr; size_t fbElems = 0;
+  void* wfBlob = nullptr; size_t wfBytes = 0; WfState wf{};   // wavefront path-state slots (rt_wavefront.cuh), grown on demand
+  unsigned long long* h_wfDone = nullptr;   // pinned: the frame-finished flag read back between batches of rounds
+  int wfRounds = 0;                         // rounds launched for the call in flight
+  RenderArgs wfArgs{}; const void* wfScene = nullptr; int wfPrec = 0; bool wfPending = false;  // a deferred wavefrontFinish (multi-GPU shares)
   cudaStream_t stream = nullptr;            // multi-GPU shares only (the single-device entry points use the caller's / default stream)
   cudaEvent_t evStart = nullptr, evDone = nullptr;
   ~DeviceCtx() {
     if (d_counter) cudaFree(d_counter);
     if (d_fb) cudaFree(d_fb);
+    if (wfBlob) cudaFree(wfBlob);
+    if (h_wfDone) cudaFreeHost(h_wfDone);
     if (evStart) cudaEventDestroy(evStart);
     if (evDone) cudaEventDestroy(evDone);
     if (stream) cudaStreamDestroy(stream);
@@ -383,8 +390,36 @@ bool useCoop(const HostScene& hs, uint32_t flags) {
   return hs.n_nodes >= tuneParam("RTB_COOP_MIN_NODES", 32768);
 }
 
+// split traversal / shade kernels: forced by RT_FLAG_WAVEFRONT; otherwise (RTB_WAVEFRONT=auto|0|1, default auto) for scenes whose
+// shading dominates — a light list to sample (every Lambertian bounce runs the mixture pdf) and a small BVH
+bool wavefrontCapable(const RtRenderParams& q, int instr) {
+  return instr == 0 && (q.precision == RT_PREC_F32 || q.precision == RT_PREC_MIXED) && !(q.flags & (RT_FLAG_FAST_MATH | RT_FLAG_STRICT_MATH));
+}
+bool useWavefront(const HostScene& hs, const RtRenderParams& q, int instr) {
+  if (!wavefrontCapable(q, instr) || (q.flags & RT_FLAG_NO_WAVEFRONT)) return false;
+  if (q.flags & RT_FLAG_WAVEFRONT) return true;
+  const char* v = std::getenv("RTB_WAVEFRONT");
+  if (v && v[0] == '0') return false;
+  if (v && v[0] == '1') return true;
+  return (hs.lights_root >> 28) != K_UNHITTABLE && hs.n_nodes <= 64 && hs.n_media == 0;
+}
+
+// more rounds of the wavefront until the frame-finished flag is set (blocks the host; the first batch was queued by renderLaunch)
+int wavefrontFinish(const HostScene& hs, DeviceCtx* c, const RenderArgs& a, const void* dsc, int prec, cudaStream_t st) {
+  for (;;) {
+    CU(cudaMemcpyAsync(c->h_wfDone, c->wf.ctl + 2, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (*c->h_wfDone) return RT_OK;
+    cudaError_t ce = launchWavefront(prec, dsc, a, c->wf, hs.stackDepth, c->numSMs, 32, false, st, nullptr);
+    if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("wavefront launch: ") + cudaGetErrorString(ce));
+    c->wfRounds += 32;
+  }
+}
+
 int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, double* d_out, cudaStream_t st, int instr, int* gridOut, const PathLog* plog = nullptr,
-                 uint32_t* kindOut = nullptr) {
+                 uint32_t* kindOut = nullptr, bool wfDefer = false) {
+  if ((q.flags & RT_FLAG_WAVEFRONT) && !wavefrontCapable(q, instr))
+    return fail(RT_ERR_UNSUPPORTED, "RT_FLAG_WAVEFRONT: fp32 / mixed arithmetic with literal math and no instrumentation only");
   if ((q.flags & RT_FLAG_COOP) && !hs.coopEligible)
     return fail(RT_ERR_UNSUPPORTED, "RT_FLAG_COOP: the scene is not eligible for the scan-stream traversal (world must be a BVH of spheres / rects, light list one primitive)");
   const void* dsc = nullptr;
@@ -419,6 +454,33 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
   const bool coop = useCoop(hs, q.flags);
   if (kindOut) *kindOut = coop ? 1u : 0u;
   cudaError_t ce;
+  if (!coop && useWavefront(hs, q, instr)) {
+    // slots: enough to keep every resident traversal lane fed several times per round, never more than chunks of paths
+    const unsigned long long maxP = (unsigned long long)c->numSMs * 8ull * kBlock * tuneParam("RTB_WF_SLOTS_PER_LANE", 4);
+    a.wfChunk = (uint32_t)std::max<unsigned long long>(1, std::min<unsigned long long>(32, a.total_paths / maxP));
+    unsigned long long P = std::min(maxP, (a.total_paths + a.wfChunk - 1) / a.wfChunk);
+    P = (P + kBlock - 1) / kBlock * kBlock;
+    const size_t bytes = wfLayout((uint32_t)P, nullptr, nullptr);
+    if (c->wfBytes < bytes) {
+      if (c->wfBlob) cudaFree(c->wfBlob);
+      c->wfBlob = nullptr; c->wfBytes = 0;
+      CU(cudaMalloc(&c->wfBlob, bytes));
+      c->wfBytes = bytes;
+    }
+    if (!c->h_wfDone) CU(cudaHostAlloc(reinterpret_cast<void**>(&c->h_wfDone), sizeof(unsigned long long), cudaHostAllocDefault));
+    wfLayout((uint32_t)P, static_cast<char*>(c->wfBlob), &c->wf);
+    a.wfMedia = hs.n_media > 0 ? 1u : 0u;
+    a.shadeMin = tuneParam("RTB_WF_ITEM_MIN", 8);
+    const unsigned long long lanes = (unsigned long long)c->numSMs * 8ull * kBlock;
+    a.chunk = (uint32_t)std::max<unsigned long long>(32, std::min<unsigned long long>(256, P / std::max<unsigned long long>(1, lanes / 32 * 4)));
+    const int rounds0 = (int)std::min<unsigned long long>(4096, a.total_paths * tuneParam("RTB_WF_EST_BOUNCES", 6) / P + 56);
+    ce = launchWavefront((int)q.precision, dsc, a, c->wf, hs.stackDepth, c->numSMs, rounds0, true, st, gridOut);
+    if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("wavefront launch: ") + cudaGetErrorString(ce));
+    c->wfRounds = rounds0;
+    if (kindOut) *kindOut = 2u;
+    if (wfDefer) { c->wfArgs = a; c->wfScene = dsc; c->wfPrec = (int)q.precision; c->wfPending = true; return RT_OK; }
+    return wavefrontFinish(hs, c, a, dsc, (int)q.precision, st);
+  }
   if (coop && (q.flags & RT_FLAG_STRICT_MATH)) ce = launchRenderCoop<MATH_STRICT>((int)q.precision, instr, dsc, a, c->numSMs, st, gridOut);
   else if (coop) ce = launchRenderCoop<MATH_LITERAL>((int)q.precision, instr, dsc, a, c->numSMs, st, gridOut);
   else if (q.flags & RT_FLAG_FAST_MATH) ce = launchRender<MATH_FAST>((int)q.precision, instr == 3 ? 0 : instr, dsc, a, hs.stackDepth, c->numSMs, st, gridOut);
@@ -526,7 +588,15 @@ int renderMulti(SceneEntry* e, const RtRenderParams& q, int nGpus, double* out, 
     CU(cudaSetDevice(devs[k]));
     CU(cudaMemsetAsync(ctx[k]->d_fb, 0, elems * sizeof(double), ctx[k]->stream));
     CU(cudaEventRecord(ctx[k]->evStart, ctx[k]->stream));
-    if ((rc = renderLaunch(e->hs, ctx[k], qk, ctx[k]->d_fb, ctx[k]->stream, 0, nullptr, nullptr, &kernelKind))) return rc;
+    ctx[k]->wfPending = false;
+    if ((rc = renderLaunch(e->hs, ctx[k], qk, ctx[k]->d_fb, ctx[k]->stream, 0, nullptr, nullptr, &kernelKind, /*wfDefer=*/true))) return rc;
+    if (!ctx[k]->wfPending) CU(cudaEventRecord(ctx[k]->evDone, ctx[k]->stream));
+  }
+  for (int k = 0; k < n; ++k) {  // wavefront shares: every device has its first batch of rounds queued; top them up until each frame is finished
+    if (!ctx[k]->wfPending) continue;
+    CU(cudaSetDevice(devs[k]));
+    if ((rc = wavefrontFinish(e->hs, ctx[k], ctx[k]->wfArgs, ctx[k]->wfScene, ctx[k]->wfPrec, ctx[k]->stream))) return rc;
+    ctx[k]->wfPending = false;
     CU(cudaEventRecord(ctx[k]->evDone, ctx[k]->stream));
   }
   // reduction onto the root
@@ -602,7 +672,7 @@ int renderMulti(SceneEntry* e, const RtRenderParams& q, int nGpus, double* out, 
     cudaEventElapsedTime(&ms, evs.ev[1], evs.ev[2]); stats->d2h_ms = ms;
     stats->samples = (uint64_t)(q.row1 - q.row0) * (q.col1 - q.col0) * q.sample_count;
     stats->launches = (uint64_t)n + (kind == RT_REDUCE_PEER ? 1 : 0);
-    stats->gpus = (uint32_t)n; stats->reduce_kind = kind; stats->replicate_ms = replicateMs; stats->kernel_kind = kernelKind;
+    stats->gpus = (uint32_t)n; stats->reduce_kind = kind; stats->replicate_ms = replicateMs; stats->kernel_kind = kernelKind; stats->rounds = kernelKind == 2 ? (uint32_t)ctx[0]->wfRounds : 0u;
   }
   return RT_OK;
 }
@@ -667,7 +737,7 @@ int renderHost(rt_scene_t scene, const RtRenderParams* params, double* out, RtSt
     cudaEventElapsedTime(&ms, e1, e2); stats->d2h_ms = ms;
     stats->samples = (uint64_t)paths;
     stats->launches = q.sample_count ? 1 : 0;
-    stats->gpus = 1; stats->kernel_kind = kernelKind;
+    stats->gpus = 1; stats->kernel_kind = kernelKind; stats->rounds = kernelKind == 2 ? (uint32_t)c->wfRounds : 0u;
     unsigned long long cc[kCtrTotal];
     CU(cudaMemcpy(cc, c->d_counter, sizeof(cc), cudaMemcpyDeviceToHost));
     if (instr == 1) {

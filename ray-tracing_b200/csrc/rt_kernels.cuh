@@ -27,6 +27,7 @@ template <> struct MinBlocks<double> { static constexpr int v = 1; };
 #include "rt_render_kernel.inl"
 }  // namespace rtb
 #include "rt_coop.cuh"
+#include "rt_wavefront.cuh"
 namespace rtb {
 
 template <class T, int MODE>

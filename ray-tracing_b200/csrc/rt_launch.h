@@ -21,7 +21,26 @@ struct RenderArgs {
   unsigned long long* ctr;         // device: kWorkCounters algorithmic-work counters + kSchedCounters scheduler statistics (INSTR=1) or null
   double* out;                     // device: double[H*W*3] radiance sums, accumulated with atomicAdd
   uint32_t* plogPrim; double* plogT; uint32_t plogStride;  // INSTR=3: per-path bounce log [total_paths][plogStride]
+  uint32_t wfChunk;                // wavefront: consecutive path indices (= consecutive samples of a pixel) a slot takes at a time
+  uint32_t wfMedia;                // wavefront: the scene has ConstantMedium (the traversal draws from the path's stream)
 };
+
+// path-state slots of the wavefront kernels (rt_wavefront.cuh): struct of arrays over P slots, one device allocation
+struct WfState {
+  uint32_t P, pad;
+  float *ox, *oy, *oz, *dx, *dy, *dz, *time;  // the item's ray (world frame) and the path's shutter time
+  float *bx, *by, *bz;                        // throughput
+  unsigned long long *rngS, *rngG;
+  uint32_t *depth, *phase;
+  float *v2, *spdf;                           // WF_LPDF: cosine-pdf value and scatteringPdf of the sampled direction (Lib.hs:374-382, 874-878)
+  float *rT, *rW; uint32_t *rPrim, *rFlags, *rChain;  // result: t, light-pdf weight, primitive, Trav flags, frames of the hit [4][P]
+  double* acc; uint32_t* accPix;              // per-slot radiance accumulator of its current pixel [3][P]
+  unsigned long long* chunkNext; uint32_t* chunkLeft;  // the slot's chunk of consecutive path indices
+  unsigned long long* ctl;                    // [0] traversal cursor over slots, [1] live slots after the last shade, [2] done, [3] next free path index
+};
+size_t wfLayout(uint32_t P, char* base, WfState* out);  // fills the pointers for a blob at `base` (may be null: size only); returns bytes
+// `rounds` rounds of (shade, end-of-round, traverse) on `st`, preceded by the slot initialisation when `init`; prec 0 / 1 only
+cudaError_t launchWavefront(int prec, const void* dscene, const RenderArgs& a, const WfState& w, int stackDepth, int numSMs, int rounds, bool init, cudaStream_t st, int* gridOut);
 
 struct TraceArgs {
   uint32_t n, logStride;

@@ -38,6 +38,55 @@ cudaError_t launchDivSelftest(unsigned long long n, unsigned long long seed, uns
   return cudaGetLastError();
 }
 
+// ---- wavefront launcher (literal arithmetic only)
+size_t wfLayout(uint32_t P, char* base, WfState* out) {
+  size_t off = 0;
+  auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += (bytes + 255) & ~(size_t)255; return p; };
+  WfState w{};
+  w.P = P;
+  float** f[] = {&w.ox, &w.oy, &w.oz, &w.dx, &w.dy, &w.dz, &w.time, &w.bx, &w.by, &w.bz, &w.v2, &w.spdf, &w.rT, &w.rW};
+  for (float** q : f) *q = reinterpret_cast<float*>(take((size_t)P * 4));
+  w.rngS = reinterpret_cast<unsigned long long*>(take((size_t)P * 8)); w.rngG = reinterpret_cast<unsigned long long*>(take((size_t)P * 8));
+  uint32_t** u[] = {&w.depth, &w.phase, &w.rPrim, &w.rFlags, &w.accPix, &w.chunkLeft};
+  for (uint32_t** q : u) *q = reinterpret_cast<uint32_t*>(take((size_t)P * 4));
+  w.rChain = reinterpret_cast<uint32_t*>(take((size_t)P * 4 * kMaxFrames));
+  w.acc = reinterpret_cast<double*>(take((size_t)P * 8 * 3));
+  w.chunkNext = reinterpret_cast<unsigned long long*>(take((size_t)P * 8));
+  w.ctl = reinterpret_cast<unsigned long long*>(take(kWfCtlWords * 8));
+  if (out) *out = w;
+  return off;
+}
+template <class S>
+static cudaError_t launchWavefrontT(const DScene<float>& sc, const RenderArgs& a, const WfState& w, int stackDepth, int numSMs, int rounds, bool init, cudaStream_t st, int* gridOut) {
+  auto trav = wfTraverseKernel<float, S>;
+  auto shade = wfShadeKernel<float>;
+  const size_t smemT = (size_t)columnWords<float>((uint32_t)stackDepth, a.lightCap) * kBlock * sizeof(uint32_t) + (kBlock / 32) * 16;
+  const size_t smemS = (size_t)extraWords<float>() * kBlock * sizeof(uint32_t);
+  cudaError_t e = cudaFuncSetAttribute(trav, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemT);
+  if (e != cudaSuccess) return e;
+  int perSM = 0;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, trav, kBlock, smemT);
+  if (e != cudaSuccess) return e;
+  if (perSM < 1) perSM = 1;
+  if (const char* v = std::getenv("RTB_WF_BLOCKS_PER_SM")) perSM = std::max(1, std::min(perSM, std::atoi(v)));
+  const int grid = std::max(1, std::min(numSMs * perSM, (int)((w.P + kBlock - 1) / kBlock)));
+  if (gridOut) *gridOut = grid;
+  RenderArgs b = a; b.stackCap = (uint32_t)stackDepth;
+  if (init) wfInitKernel<<<(w.P + 255) / 256, 256, 0, st>>>(w);
+  for (int r = 0; r < rounds; ++r) {
+    shade<<<(w.P + kBlock - 1) / kBlock, kBlock, smemS, st>>>(sc, b, w);
+    wfEndRoundKernel<<<1, 1, 0, st>>>(w.ctl);
+    trav<<<grid, kBlock, smemT, st>>>(sc, b, w);
+  }
+  return cudaGetLastError();
+}
+cudaError_t launchWavefront(int prec, const void* dscene, const RenderArgs& a, const WfState& w, int stackDepth, int numSMs, int rounds, bool init, cudaStream_t st, int* gridOut) {
+  const auto& sc = *static_cast<const DScene<float>*>(dscene);
+  if (prec == 0) return launchWavefrontT<float>(sc, a, w, stackDepth, numSMs, rounds, init, st, gridOut);
+  if (prec == 1) return launchWavefrontT<double>(sc, a, w, stackDepth, numSMs, rounds, init, st, gridOut);
+  return cudaErrorInvalidValue;
+}
+
 template cudaError_t launchRender<MATH_LITERAL>(int, int, const void*, const RenderArgs&, int, int, cudaStream_t, int*);
 template cudaError_t launchTrace<MATH_LITERAL>(int, const void*, const TraceArgs&, int, cudaStream_t);
 template cudaError_t launchRenderCoop<MATH_LITERAL>(int, int, const void*, const RenderArgs&, int, cudaStream_t, int*);

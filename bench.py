@@ -193,7 +193,7 @@ def roofline_block(scene, W, H, spp, synth_n, work, kernel_ms, peaks, fp32, fast
         # the one memory-side config: 1 M spheres = 33.5 MB of nodes + 16 MB of spheres, L2-resident on B200 (126 MB): node / leaf
         # fetch bandwidth against the measured L2 and HBM peaks
         return {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
-                "traffic": mem["dram_bytes_per_launch"], "kernel": "renderKernel", "kernel_ms": kernel_ms, "peak_source": mem["hbm_peak_source"],
+                "traffic": mem["dram_bytes_per_launch"], "kernel": work.get("kernel", "renderKernel"), "kernel_ms": kernel_ms, "peak_source": mem["hbm_peak_source"],
                 "l2": {"achieved_algorithmic_gbs": ach_gbs, "peak": mem["l2_peak_gbs"], "frac": ach_gbs / mem["l2_peak_gbs"] if mem["l2_peak_gbs"] else None,
                        "peak_source": "profiles/fp32_peak.json l2_read_gbs (tools/fp32_peak.cu, 48 MB buffer)"},
                 "memory": mem, "algorithmic_flops_per_sample": work["flops"], "per_sample": work["per_sample"],
@@ -204,7 +204,7 @@ def roofline_block(scene, W, H, spp, synth_n, work, kernel_ms, peaks, fp32, fast
                            ("FFMA issue rate x 2" if fast else "non-FMA FADD/FMUL issue rate, 1 flop per lane-instruction — the literal build is compiled --fmad=false, "
                             "so no algorithmic op can ride an FMA"),
             "frac_of_ffma_peak": ach_tf / ffma_peak, "ffma_peak_tflops": ffma_peak,
-            "kernel": "renderKernel", "kernel_ms": kernel_ms, "algorithmic_flops_per_sample": work["flops"],
+            "kernel": work.get("kernel", "renderKernel"), "kernel_ms": kernel_ms, "algorithmic_flops_per_sample": work["flops"],
             "flops_traversal_per_sample": work["flops_traversal"], "flops_shading_per_sample": work["flops_shading"], "per_sample": work["per_sample"],
             "memory": mem,
             "note": "scene is L1/L2-resident; the binding limit is FP32/ALU issue under divergence (ncu: smsp__issue_active, "
@@ -237,6 +237,7 @@ def measure(cx, scene, spp, steps, warmup, synth_n=1000, size=None, cpu=True, e2
         else:
             _, st = ds.render(W, H, 2, counted=True, seed=99, precision=prec, flags=flags)
         work = algorithmic_work(st["counters"])
+        work["kernel"] = ds.render(W, H, 1, region=(0, 1, 0, min(W, 8)), precision=prec, flags=flags)[1]["kernel"]  # which kernel this scene selects
 
     def sync():
         if world > 1:

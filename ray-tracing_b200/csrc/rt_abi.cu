@@ -410,8 +410,8 @@ int wavefrontFinish(const HostScene& hs, DeviceCtx* c, const RenderArgs& a, cons
     CU(cudaMemcpyAsync(c->h_wfDone, c->wf.ctl + 2, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     if (*c->h_wfDone) return RT_OK;
-    // every round finishes at least one bounce of every live path: a frame needs at most paths * (maxDepth + 1) / slots + maxDepth rounds
-    const unsigned long long bound = a.total_paths / std::max(1u, c->wf.P) * (a.maxDepth + 1ull) * 2ull + 4ull * (a.maxDepth + 2ull) + 64ull;
+    // every round finishes at least one bounce of every live path: a frame needs at most paths * (maxDepth + 1) / slots rounds plus the tail of one chunk
+    const unsigned long long bound = a.total_paths / std::max(1u, c->wf.P) * (a.maxDepth + 1ull) * 2ull + 2ull * a.wfChunk * (a.maxDepth + 2ull) + 64ull;
     if ((unsigned long long)c->wfRounds > bound) return fail(RT_ERR_CUDA, "wavefront: the frame did not finish within its round bound (internal error)");
     cudaError_t ce = launchWavefront(prec, dsc, a, c->wf, hs.stackDepth, c->numSMs, 32, false, st, nullptr);
     if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("wavefront launch: ") + cudaGetErrorString(ce));

@@ -162,8 +162,9 @@ extern "C" int rt_bvh_build(uint32_t n, const double* leaf_box, const uint8_t* n
   BVH_CU(dTmp.alloc(std::max(tmp1, tmp2)));
   size_t tmpBytes = std::max(tmp1, tmp2);
 
-  cudaEvent_t e0, e1;
-  BVH_CU(cudaEventCreate(&e0)); BVH_CU(cudaEventCreate(&e1));
+  struct Ev { cudaEvent_t e = nullptr; ~Ev() { if (e) cudaEventDestroy(e); } } ev0, ev1;  // destroyed on every early error return too
+  BVH_CU(cudaEventCreate(&ev0.e)); BVH_CU(cudaEventCreate(&ev1.e));
+  const cudaEvent_t e0 = ev0.e, e1 = ev1.e;
   BVH_CU(cudaEventRecord(e0));
   BVH_CU(cudaMemcpy(dBox.p, leaf_box, (size_t)n * 6 * 8, cudaMemcpyHostToDevice));
   BVH_CU(cudaMemcpy(dAxis.p, node_axis, n_nodes, cudaMemcpyHostToDevice));
@@ -221,6 +222,5 @@ extern "C" int rt_bvh_build(uint32_t n, const double* leaf_box, const uint8_t* n
   BVH_CU(cudaEventRecord(e1)); BVH_CU(cudaEventSynchronize(e1));
   float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
   if (build_ms) *build_ms = ms;
-  cudaEventDestroy(e0); cudaEventDestroy(e1);
   return RT_OK;
 }

@@ -244,15 +244,18 @@ def measure(cx, scene, spp, steps, warmup, synth_n=1000, size=None, cpu=True, e2
             dist.barrier()
         torch.cuda.synchronize()
 
+    launches = []  # kernels launched per timed step (the wavefront path launches two per round)
+
     def step(i, ev=None):
         cx.flush.zero_()  # L2 flush between iterations
         fb.zero_()
         s0, n = _dist.shard_samples(total_spp, rank, world)
         if ev:
             ev[0].record()
-        ds.render_device(fb.data_ptr(), W, H, n, stream=stream, depth=50, seed=1 + i, s0=s0, precision=prec, flags=flags, total=total_spp)
+        st_ = ds.render_device(fb.data_ptr(), W, H, n, stream=stream, depth=50, seed=1 + i, s0=s0, precision=prec, flags=flags, total=total_spp, timed=bool(ev))
         if ev:
             ev[1].record()
+            launches.append(st_["launches"])
         _dist.reduce_framebuffer(fb, 0)
 
     for i in range(warmup):
@@ -279,7 +282,7 @@ def measure(cx, scene, spp, steps, warmup, synth_n=1000, size=None, cpu=True, e2
         out = {"scene": scene, "workload": SCENE_DOC[scene] if scene != "synthetic" else SCENE_DOC[scene] + "; %d spheres, %dx%d x %d spp" % (synth_n * synth_n, W, H, spp),
                "width": W, "height": H, "spp_per_gpu_per_step": spp, "steps": steps, "warmup": warmup,
                "value": value, "unit": "samples/s", "ms_per_step": ms / steps, "kernel_ms": kernel_ms, "finite_pixel_fraction": finite_frac,
-               "roofline": roofline_block(scene, W, H, spp, synth_n, work, kernel_ms, cx.peaks, cx.fp32, args.fast), "gpu_launches": steps}
+               "roofline": roofline_block(scene, W, H, spp, synth_n, work, kernel_ms, cx.peaks, cx.fp32, args.fast), "gpu_launches": int(sum(launches))}
         if scene == "synthetic":
             out["host_scene_build_s"] = host_build_s
 
@@ -440,7 +443,7 @@ def main():
                        "seed": "randGen 1024", "lights": "HEAD", "parallelism": "spp-sharded x%d + ncclReduce (torch.distributed)" % world,
                        "l2": "flushed between steps (256 MiB write)",
                        "arithmetic": "fast-math" if args.fast else "literal (no FMA contraction, IEEE div/sqrt)", "finite_pixel_fraction": head["finite_pixel_fraction"]},
-            "roofline": head["roofline"], "e2e": e2e, "gpu_launches": args.steps, "clocks": clocks,
+            "roofline": head["roofline"], "e2e": e2e, "gpu_launches": head["gpu_launches"], "clocks": clocks,
         }
         for k in ("cpu_baseline", "strong", "sharding_check"):
             if k in head:

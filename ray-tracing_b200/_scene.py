@@ -126,7 +126,7 @@ class DeviceScene:
         p = self.params(W, H, spp, **kw)
         st = RtStats()
         _check(core().rt_render_device(self.id, C.byref(p), C.c_void_p(d_ptr), C.c_void_p(stream), C.byref(st) if timed else None))
-        return st.kernel_ms if timed else None
+        return dict(kernel_ms=st.kernel_ms, launches=int(st.launches), rounds=int(st.rounds), kernel=["renderKernel", "renderKernelCoop", "wavefront"][st.kernel_kind]) if timed else None
 
     def render_pathlog(self, W, H, spp, max_bounces=50, **kw):
         """-> (radiance sums, prim_log uint32 [paths, max_bounces] (0xfffffffe = bounce not reached, 0xffffffff = miss), t_log float64)"""

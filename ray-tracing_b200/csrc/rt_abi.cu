@@ -68,7 +68,7 @@ struct DeviceCtx {
   unsigned long long* d_counter = nullptr;  // kCtrTotal words: [0] path counter, work counters, scheduler statistics, tail stamps (rt_device.cuh kCtr*)
   double* d_fb = nullptr; size_t fbElems = 0;
   void* wfBlob = nullptr; size_t wfBytes = 0; WfState wf{};   // wavefront path-state slots (rt_wavefront.cuh), grown on demand
-  unsigned long long* h_wfDone = nullptr;   // pinned: the frame-finished flag read back between batches of rounds
+  unsigned long long* h_wfCtl = nullptr;    // pinned: {frame finished, next free path index} read back between batches of rounds
   int wfRounds = 0;                         // rounds launched for the call in flight
   RenderArgs wfArgs{}; const void* wfScene = nullptr; int wfPrec = 0; bool wfPending = false;  // a deferred wavefrontFinish (multi-GPU shares)
   cudaStream_t stream = nullptr;            // multi-GPU shares only (the single-device entry points use the caller's / default stream)
@@ -77,7 +77,7 @@ struct DeviceCtx {
     if (d_counter) cudaFree(d_counter);
     if (d_fb) cudaFree(d_fb);
     if (wfBlob) cudaFree(wfBlob);
-    if (h_wfDone) cudaFreeHost(h_wfDone);
+    if (h_wfCtl) cudaFreeHost(h_wfCtl);
     if (evStart) cudaEventDestroy(evStart);
     if (evDone) cudaEventDestroy(evDone);
     if (stream) cudaStreamDestroy(stream);
@@ -407,15 +407,20 @@ bool useWavefront(const HostScene& hs, const RtRenderParams& q, int instr) {
 // more rounds of the wavefront until the frame-finished flag is set (blocks the host; the first batch was queued by renderLaunch)
 int wavefrontFinish(const HostScene& hs, DeviceCtx* c, const RenderArgs& a, const void* dsc, int prec, cudaStream_t st) {
   for (;;) {
-    CU(cudaMemcpyAsync(c->h_wfDone, c->wf.ctl + 2, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(c->h_wfCtl, c->wf.ctl + 2, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));  // done, next free path index
     CU(cudaStreamSynchronize(st));
-    if (*c->h_wfDone) return RT_OK;
+    if (c->h_wfCtl[0]) return RT_OK;
     // every round finishes at least one bounce of every live path: a frame needs at most paths * (maxDepth + 1) / slots rounds plus the tail of one chunk
     const unsigned long long bound = a.total_paths / std::max(1u, c->wf.P) * (a.maxDepth + 1ull) * 2ull + 2ull * a.wfChunk * (a.maxDepth + 2ull) + 64ull;
     if ((unsigned long long)c->wfRounds > bound) return fail(RT_ERR_CUDA, "wavefront: the frame did not finish within its round bound (internal error)");
-    cudaError_t ce = launchWavefront(prec, dsc, a, c->wf, hs.stackDepth, c->numSMs, 32, false, st, nullptr);
+    // size the next batch from the progress so far: paths handed out per round, then the drain of the last paths
+    const double handed = (double)std::min<unsigned long long>(c->h_wfCtl[1], a.total_paths);
+    const double frac = handed / (double)a.total_paths;
+    int more = 32;
+    if (frac > 0.02 && frac < 1.0) more = (int)std::min(4096.0, (double)c->wfRounds * (1.0 - frac) / frac * 1.05 + 16.0);
+    cudaError_t ce = launchWavefront(prec, dsc, a, c->wf, hs.stackDepth, c->numSMs, more, false, st, nullptr);
     if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("wavefront launch: ") + cudaGetErrorString(ce));
-    c->wfRounds += 32;
+    c->wfRounds += more;
   }
 }
 
@@ -470,13 +475,13 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
       CU(cudaMalloc(&c->wfBlob, bytes));
       c->wfBytes = bytes;
     }
-    if (!c->h_wfDone) CU(cudaHostAlloc(reinterpret_cast<void**>(&c->h_wfDone), sizeof(unsigned long long), cudaHostAllocDefault));
+    if (!c->h_wfCtl) CU(cudaHostAlloc(reinterpret_cast<void**>(&c->h_wfCtl), 2 * sizeof(unsigned long long), cudaHostAllocDefault));
     wfLayout((uint32_t)P, static_cast<char*>(c->wfBlob), &c->wf);
     a.wfMedia = hs.n_media > 0 ? 1u : 0u;
     a.shadeMin = tuneParam("RTB_WF_ITEM_MIN", 8);
     const unsigned long long lanes = (unsigned long long)c->numSMs * 8ull * kBlock;
     a.chunk = (uint32_t)std::max<unsigned long long>(32, std::min<unsigned long long>(256, P / std::max<unsigned long long>(1, lanes / 32 * 4)));
-    const int rounds0 = (int)std::min<unsigned long long>(4096, a.total_paths * tuneParam("RTB_WF_EST_BOUNCES", 6) / P + 56);
+    const int rounds0 = (int)std::min<unsigned long long>(4096, a.total_paths * tuneParam("RTB_WF_EST_BOUNCES", 4) / P + 24);
     ce = launchWavefront((int)q.precision, dsc, a, c->wf, hs.stackDepth, c->numSMs, rounds0, true, st, gridOut);
     if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("wavefront launch: ") + cudaGetErrorString(ce));
     c->wfRounds = rounds0;
@@ -741,6 +746,7 @@ int renderHost(rt_scene_t scene, const RtRenderParams* params, double* out, RtSt
     stats->samples = (uint64_t)paths;
     stats->launches = q.sample_count ? 1 : 0;
     stats->gpus = 1; stats->kernel_kind = kernelKind; stats->rounds = kernelKind == 2 ? (uint32_t)c->wfRounds : 0u;
+    if (kernelKind == 2) stats->launches = 1ull + 2ull * (uint64_t)c->wfRounds;
     unsigned long long cc[kCtrTotal];
     CU(cudaMemcpy(cc, c->d_counter, sizeof(cc), cudaMemcpyDeviceToHost));
     if (instr == 1) {
@@ -1005,6 +1011,7 @@ int rt_render_device(rt_scene_t scene, const RtRenderParams* params, double* d_o
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
     stats->kernel_ms = ms; stats->samples = (uint64_t)(q.row1 - q.row0) * (q.col1 - q.col0) * q.sample_count; stats->launches = q.sample_count ? 1 : 0;
     stats->gpus = 1; stats->gpu_kernel_ms[0] = ms; stats->kernel_kind = kernelKind;
+    if (kernelKind == 2) { stats->rounds = (uint32_t)e->main.wfRounds; stats->launches = 1ull + 2ull * (uint64_t)e->main.wfRounds; }
   }
   return RT_OK;
 }

@@ -36,10 +36,10 @@ struct WfState {
   float *rT, *rW; uint32_t *rPrim, *rFlags, *rChain;  // result: t, light-pdf weight, primitive, Trav flags, frames of the hit [4][P]
   double* acc; uint32_t* accPix;              // per-slot radiance accumulator of its current pixel [3][P]
   unsigned long long* chunkNext; uint32_t* chunkLeft;  // the slot's chunk of consecutive path indices
-  unsigned long long* ctl;                    // [0] traversal cursor over slots, [1] live slots after the last shade, [2] done, [3] next free path index
+  unsigned long long* ctl;                    // [0] traversal cursor over slots, [1] live slots of the shade in flight, [2] done, [3] next free path index, [4] shade blocks finished
 };
 size_t wfLayout(uint32_t P, char* base, WfState* out);  // fills the pointers for a blob at `base` (may be null: size only); returns bytes
-// `rounds` rounds of (shade, end-of-round, traverse) on `st`, preceded by the slot initialisation when `init`; prec 0 / 1 only
+// `rounds` rounds of (shade, traverse) on `st`, preceded by the slot initialisation when `init`; prec 0 / 1 only
 cudaError_t launchWavefront(int prec, const void* dscene, const RenderArgs& a, const WfState& w, int stackDepth, int numSMs, int rounds, bool init, cudaStream_t st, int* gridOut);
 
 struct TraceArgs {

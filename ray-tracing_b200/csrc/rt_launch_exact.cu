@@ -75,7 +75,6 @@ static cudaError_t launchWavefrontT(const DScene<float>& sc, const RenderArgs& a
   if (init) wfInitKernel<<<(w.P + 255) / 256, 256, 0, st>>>(w);
   for (int r = 0; r < rounds; ++r) {
     shade<<<(w.P + kBlock - 1) / kBlock, kBlock, smemS, st>>>(sc, b, w);
-    wfEndRoundKernel<<<1, 1, 0, st>>>(w.ctl);
     trav<<<grid, kBlock, smemT, st>>>(sc, b, w);
   }
   return cudaGetLastError();

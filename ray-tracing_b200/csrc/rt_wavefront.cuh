@@ -244,15 +244,18 @@ __global__ void __launch_bounds__(kBlock) wfShadeKernel(const __grid_constant__ 
       }
     }
   }
-  // live slots of this round (block-aggregated); the host reads ctl[1] after a batch of rounds, wfEndRound turns it into `done`
+  // live slots of this round, block-aggregated; the LAST block to finish closes the round: no live slot left -> done (the later
+  // launches of the batch return at once), else the live count is reset for the next round
   const int nLive = __syncthreads_count(live);
-  if (threadIdx.x == 0 && nLive) atomicAdd(w.ctl + 1, (unsigned long long)nLive);
-}
-
-// closes a round: no live slot left -> done (the later launches of the batch return at once), else reset the live count
-static __global__ void wfEndRoundKernel(unsigned long long* ctl) {
-  if (ctl[2]) return;
-  if (ctl[1] == 0) ctl[2] = 1; else ctl[1] = 0;
+  if (threadIdx.x == 0) {
+    if (nLive) atomicAdd(w.ctl + 1, (unsigned long long)nLive);
+    __threadfence();
+    if (atomicAdd(w.ctl + 4, 1ull) == (unsigned long long)gridDim.x - 1ull) {
+      __threadfence();
+      if (atomicExch(w.ctl + 1, 0ull) == 0ull) w.ctl[2] = 1ull;
+      w.ctl[4] = 0ull;
+    }
+  }
 }
 
 // first launch of a frame: every slot is new

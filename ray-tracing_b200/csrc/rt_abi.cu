@@ -478,6 +478,7 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
     if (!c->h_wfCtl) CU(cudaHostAlloc(reinterpret_cast<void**>(&c->h_wfCtl), 2 * sizeof(unsigned long long), cudaHostAllocDefault));
     wfLayout((uint32_t)P, static_cast<char*>(c->wfBlob), &c->wf);
     a.wfMedia = hs.n_media > 0 ? 1u : 0u;
+    a.wfSort = tuneParam("RTB_WF_SORT", 1);
     a.shadeMin = tuneParam("RTB_WF_ITEM_MIN", 8);
     const unsigned long long lanes = (unsigned long long)c->numSMs * 8ull * kBlock;
     a.chunk = (uint32_t)std::max<unsigned long long>(32, std::min<unsigned long long>(256, P / std::max<unsigned long long>(1, lanes / 32 * 4)));

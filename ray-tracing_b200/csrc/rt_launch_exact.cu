@@ -61,8 +61,10 @@ static cudaError_t launchWavefrontT(const DScene<float>& sc, const RenderArgs& a
   auto trav = wfTraverseKernel<float, S>;
   auto shade = wfShadeKernel<float>;
   const size_t smemT = (size_t)columnWords<float>((uint32_t)stackDepth, a.lightCap) * kBlock * sizeof(uint32_t) + (kBlock / 32) * 16;
-  const size_t smemS = (size_t)extraWords<float>() * kBlock * sizeof(uint32_t);
+  const size_t smemS = ((size_t)extraWords<float>() * kBlock * (kShadeBlock / kBlock) + kShadeBlock + 8) * sizeof(uint32_t);
   cudaError_t e = cudaFuncSetAttribute(trav, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemT);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(shade, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemS);
   if (e != cudaSuccess) return e;
   int perSM = 0;
   e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, trav, kBlock, smemT);
@@ -74,7 +76,7 @@ static cudaError_t launchWavefrontT(const DScene<float>& sc, const RenderArgs& a
   RenderArgs b = a; b.stackCap = (uint32_t)stackDepth;
   if (init) wfInitKernel<<<(w.P + 255) / 256, 256, 0, st>>>(w);
   for (int r = 0; r < rounds; ++r) {
-    shade<<<(w.P + kBlock - 1) / kBlock, kBlock, smemS, st>>>(sc, b, w);
+    shade<<<(w.P + kShadeBlock - 1) / kShadeBlock, kShadeBlock, smemS, st>>>(sc, b, w);
     trav<<<grid, kBlock, smemT, st>>>(sc, b, w);
   }
   return cudaGetLastError();

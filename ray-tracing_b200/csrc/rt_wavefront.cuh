@@ -143,19 +143,58 @@ __global__ void __launch_bounds__(kBlock, 8) wfTraverseKernel(const __grid_const
 }
 
 // ---- shade ---------------------------------------------------------------------------------------------------------------------------
+constexpr int kShadeBlock = 512;  // slots per shade block = the group that is sorted by material (4 column groups of kBlock threads)
+
+// what a slot's thread will execute: 0 = no hit to shade (new slot, miss, depth exhausted: accumulate / regenerate), 1 + material kind
+// for a hit, 7 = dead slot
+template <class T> RTB_D uint32_t wfShadeBin(const DScene<T>& sc, const WfState& w, uint32_t s) {
+  if (s >= w.P) return 7u;
+  const uint32_t ph = w.phase[s];
+  if (ph == WF_DEAD) return 7u;
+  if (ph == WF_NEW) return 0u;
+  const uint32_t fl = w.rFlags[s];
+  if ((fl & WF_R_NOMAIN) || !(fl & F_QHIT)) return 0u;
+  const uint32_t prim = w.rPrim[s], kind = prim >> 28, idx = prim & kIdxMask;
+  uint32_t mat;
+  if (kind == K_SPHERE) mat = __ldg(sc.sphere_mat + idx);
+  else if (kind == K_MOVING) mat = bitsOf(ldq(sc.moving + 3 * (size_t)idx + 2).y);
+  else if (kind == K_CUBOID) mat = bitsOf(ldq(sc.cuboids + 2 * (size_t)idx).w);
+  else if (kind == K_MEDIUM) mat = bitsOf(ldq(sc.media + idx).y);
+  else mat = bitsOf(ldq(sc.rects + 2 * (size_t)idx + 1).y);
+  return 1u + bitsOf(ldq(sc.mats + mat).x);
+}
+
 template <class T>
-__global__ void __launch_bounds__(kBlock) wfShadeKernel(const __grid_constant__ DScene<T> sc, const __grid_constant__ RenderArgs a, const __grid_constant__ WfState w) {
+__global__ void __launch_bounds__(kShadeBlock) wfShadeKernel(const __grid_constant__ DScene<T> sc, const __grid_constant__ RenderArgs a, const __grid_constant__ WfState w) {
   extern __shared__ uint32_t smem[];
   if (w.ctl[2]) return;
-  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s == 0) w.ctl[0] = 0;  // the next traversal starts at slot 0 (the previous traversal has finished: stream order)
+  if (blockIdx.x == 0 && threadIdx.x == 0) w.ctl[0] = 0;  // the next traversal starts at slot 0 (the previous traversal has finished: stream order)
+  // ---- the block's slots sorted by what their threads will execute (a counting sort in shared memory): warps shade one material
+  //      instead of running every material's code with a handful of lanes each.  Which thread takes which slot changes nothing per path.
+  const uint32_t colWords = (uint32_t)extraWords<T>() * kBlock;
+  uint32_t* perm = smem + (kShadeBlock / kBlock) * colWords;
+  uint32_t* cnt = perm + kShadeBlock;
+  const uint32_t sBase = blockIdx.x * (uint32_t)kShadeBlock;
+  if (threadIdx.x < 8) cnt[threadIdx.x] = 0;
+  __syncthreads();
+  uint32_t s = sBase + threadIdx.x;
+  if (a.wfSort) {
+    const uint32_t myBin = wfShadeBin<T>(sc, w, s);
+    const uint32_t myRank = atomicAdd(&cnt[myBin], 1u);
+    __syncthreads();
+    uint32_t off = 0;
+    for (uint32_t b = 0; b < myBin; ++b) off += cnt[b];
+    perm[off + myRank] = threadIdx.x;
+    __syncthreads();
+    s = sBase + perm[threadIdx.x];
+  }
   bool live = false;
   if (s < w.P) {
     uint32_t ph = w.phase[s];
     if (ph != WF_DEAD) {
       Instr<0> ins;
       Trav<T> tr;
-      tr.col = smem + threadIdx.x;
+      tr.col = smem + (threadIdx.x / kBlock) * colWords + (threadIdx.x % kBlock);
       tr.sp = 0; tr.tmin = 0; tr.inv = mk<T>(0, 0, 0); tr.cur = kEmpty;
       stD(&tr.xw(XW_ACC + 0), tr.stride, 0.0); stD(&tr.xw(XW_ACC + 2), tr.stride, 0.0); stD(&tr.xw(XW_ACC + 4), tr.stride, 0.0);
       PathState<T> ps;

@@ -10,11 +10,11 @@ hs = pkg.HostScene("cornell"); ds = hs.upload(W, H)
 ds.render(W, H, 8, seed=1, flags=pkg.FLAG_WAVEFRONT)
 base = min(ds.render(W, H, spp, seed=2 + i, flags=pkg.FLAG_NO_WAVEFRONT)[1]["kernel_ms"] for i in range(2))
 print("renderKernel %.2f ms %.1f Msamples/s" % (base, W * H * spp / base / 1e3), flush=True)
-for slots in (2, 4, 8, 16, 32):
-    for item in (4, 8, 16):
-        for bps in (8, 6):
-            os.environ.update(RTB_WF_SLOTS_PER_LANE=str(slots), RTB_WF_ITEM_MIN=str(item), RTB_WF_BLOCKS_PER_SM=str(bps))
+for slots, item, bps, sort in [(s_, i_, 8, 1) for s_ in (2, 4, 8, 16, 32) for i_ in (4, 8, 16)] + [(4, 8, 6, 1), (8, 8, 6, 1), (4, 8, 8, 0), (8, 8, 8, 0), (16, 8, 8, 0)]:
+    if True:
+        if True:
+            os.environ.update(RTB_WF_SLOTS_PER_LANE=str(slots), RTB_WF_ITEM_MIN=str(item), RTB_WF_BLOCKS_PER_SM=str(bps), RTB_WF_SORT=str(sort))
             ds.render(W, H, 8, seed=1, flags=pkg.FLAG_WAVEFRONT)
             rs = [ds.render(W, H, spp, seed=2 + i, flags=pkg.FLAG_WAVEFRONT)[1] for i in range(2)]
             best = min(r["kernel_ms"] for r in rs)
-            print("slots/lane %2d item_min %2d blocks/SM %d: %8.2f ms %7.1f Msamples/s rounds %d" % (slots, item, bps, best, W * H * spp / best / 1e3, rs[0]["rounds"]), flush=True)
+            print("slots/lane %2d item_min %2d blocks/SM %d sort %d: %8.2f ms %7.1f Msamples/s rounds %d" % (slots, item, bps, sort, best, W * H * spp / best / 1e3, rs[0]["rounds"]), flush=True)

@@ -449,6 +449,8 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
   const unsigned long long chunkMin = std::max(1u, tuneParam("RTB_CHUNK_MIN", 4));
   while (chunk > chunkMin && a.total_paths / chunk < warps * 8ull) chunk /= 2;
   a.chunk = (uint32_t)chunk;
+  a.chunkMin = (uint32_t)std::min<unsigned long long>(chunk, std::max(chunkMin, (unsigned long long)tuneParam("RTB_CHUNK_TAIL", 32)));
+  a.chunkDiv = (uint32_t)std::max<unsigned long long>(1, warps * tuneParam("RTB_CHUNK_DIV", 2));
   // scheduler thresholds (rt_render_kernel.inl): single rects are cheap steps and worth running for 3 lanes, cuboid-heavy scenes batch
   // 6; media make the rare class frequent (3 rare steps per medium visit) and worth running for 4 lanes.  Measured on the
   // reference scenes (tools/knob_sweep.py); results never depend on these.

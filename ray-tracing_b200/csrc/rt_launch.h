@@ -10,7 +10,8 @@ struct RenderArgs {
   uint32_t s0, ns;                 // sample range [s0, s0+ns)
   uint32_t maxDepth;
   uint32_t row0, row1, col0, col1; // region (rows counted from the top)
-  uint32_t chunk;                  // path indices a warp takes per atomic
+  uint32_t chunk;                  // path indices a warp takes per atomic (at most; guided: fewer towards the end of the index space)
+  uint32_t chunkMin, chunkDiv;     // smallest chunk; a warp asks for (indices left) / chunkDiv
   uint32_t stackCap;               // traversal stack entries per thread (set by the launcher)
   uint32_t lightCap;               // entries of htblPdfValue's walk stack per thread: levels of the lights BVH, 0 when the light list is no BVH
   uint32_t shadeMin, rectMin, rareMin;  // full vote: run the shade / rect+cuboid / rare class as soon as this many lanes wait for it

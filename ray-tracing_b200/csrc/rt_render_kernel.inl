@@ -256,15 +256,23 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
         uint32_t cNext = ws[2], cEnd = ws[3];
         if (cNext >= cEnd) {
           if (exhausted) break;
-          unsigned long long base = 0;
-          if (lane == 0) base = atomicAdd(a.counter, (unsigned long long)a.chunk);
-          base = __shfl_sync(0xffffffffu, base, 0);
+          // guided chunks: a.chunk path indices while plenty are left, fewer towards the end of the index space (what is left divided
+          // among the resident warps, never below a.chunkMin) so that the kernel's tail is the time of a SMALL chunk, not of a full one
+          unsigned long long base = 0; uint32_t csize = a.chunk;
+          if (lane == 0) {
+            const unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(a.counter);
+            const unsigned long long left = cur < a.total_paths ? a.total_paths - cur : 0ull;
+            const unsigned long long want = left / a.chunkDiv;
+            csize = (uint32_t)(want < a.chunkMin ? a.chunkMin : (want > a.chunk ? a.chunk : want));
+            base = atomicAdd(a.counter, (unsigned long long)csize);
+          }
+          base = __shfl_sync(0xffffffffu, base, 0); csize = __shfl_sync(0xffffffffu, csize, 0);
           if (base >= a.total_paths) {  // first warp to find the index space empty stamps the start of the kernel's tail (RtStats::tail_ms)
             if (lane == 0) atomicCAS(a.counter + kCtrTailBase, 0ull, globalTimerNs());
             exhausted = true; break;
           }
           cNext = 0;
-          cEnd = (base + a.chunk < a.total_paths) ? a.chunk : (uint32_t)(a.total_paths - base);
+          cEnd = (base + csize < a.total_paths) ? csize : (uint32_t)(a.total_paths - base);
           if (lane == 0) { ws[0] = (uint32_t)(base / a.ns); ws[1] = (uint32_t)(base % a.ns); ws[3] = cEnd; }
           __syncwarp();
         }

@@ -379,6 +379,7 @@ def main():
     ap.add_argument("--precision", type=int, default=1, help="0 fp32 (opt-in, biased on Book-1/2 scenes), 1 = RT_PREC_MIXED the production arithmetic, 2 fp64")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-per-scene", action="store_true", help="only the headline workload (profiling runs)")
+    ap.add_argument("--profile", action="store_true", help="under ncu: headline workload only, no e2e loop, no CPU baseline")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     W, H = SCENE_SIZE[args.scene]
@@ -414,7 +415,9 @@ def main():
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    head = measure(cx, args.scene, spp, args.steps, args.warmup, synth_n=args.synth_n, size=(W, H))
+    if args.profile:
+        args.no_per_scene = args.no_cpu_baseline = True
+    head = measure(cx, args.scene, spp, args.steps, args.warmup, synth_n=args.synth_n, size=(W, H), e2e=not args.profile)
     # the sampler runs through both timed regions of the headline workload (terminating nvidia-smi stalls the context for up to a few
     # hundred ms, which the wall-clocked end-to-end loop would see) and is stopped only here
     clocks = sampler.stop() if rank == 0 else None
@@ -434,7 +437,7 @@ def main():
                 per_scene[key] = r
 
     if rank == 0:
-        e2e = head.pop("e2e")
+        e2e = head.pop("e2e", None)
         line = {
             "metric": "samples/sec", "value": head["value"], "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

@@ -466,7 +466,7 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
   cudaError_t ce;
   if (!coop && useWavefront(hs, q, instr)) {
     // slots: enough to keep every resident traversal lane fed several times per round, never more than chunks of paths
-    const unsigned long long maxP = (unsigned long long)c->numSMs * 8ull * kBlock * tuneParam("RTB_WF_SLOTS_PER_LANE", 4);
+    const unsigned long long maxP = (unsigned long long)c->numSMs * 8ull * kBlock * tuneParam("RTB_WF_SLOTS_PER_LANE", 16);
     a.wfChunk = (uint32_t)std::max<unsigned long long>(1, std::min<unsigned long long>(32, a.total_paths / maxP));
     unsigned long long P = std::min(maxP, (a.total_paths + a.wfChunk - 1) / a.wfChunk);
     P = (P + kBlock - 1) / kBlock * kBlock;
@@ -480,7 +480,7 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
     if (!c->h_wfCtl) CU(cudaHostAlloc(reinterpret_cast<void**>(&c->h_wfCtl), 2 * sizeof(unsigned long long), cudaHostAllocDefault));
     wfLayout((uint32_t)P, static_cast<char*>(c->wfBlob), &c->wf);
     a.wfMedia = hs.n_media > 0 ? 1u : 0u;
-    a.wfSort = tuneParam("RTB_WF_SORT", 1);
+    a.wfSort = tuneParam("RTB_WF_SORT", 0);  // measured: the block-level material sort costs what it saves (tools/wf_sweep.py), off by default
     a.shadeMin = tuneParam("RTB_WF_ITEM_MIN", 8);
     const unsigned long long lanes = (unsigned long long)c->numSMs * 8ull * kBlock;
     a.chunk = (uint32_t)std::max<unsigned long long>(32, std::min<unsigned long long>(256, P / std::max<unsigned long long>(1, lanes / 32 * 4)));

@@ -29,7 +29,8 @@ for spec in sys.argv[2:]:
             v = g(n); u = units[hdr.index(n)].lower()
             return v * {"ns": 1e-6, "us": 1e-3, "usecond": 1e-3, "ms": 1, "msecond": 1, "s": 1e3, "second": 1e3, "nsecond": 1e-6}.get(u, 1)
         ent["kernels"].append({"kernel": r[iK][:80], "kernel_ms": ms("gpu__time_duration.sum"), "dram_bytes_read": byts("dram__bytes_read.sum"),
-                               "dram_bytes_write": byts("dram__bytes_write.sum"), "lts_bytes": byts("lts__t_bytes.sum"), "l1tex_bytes": byts("l1tex__t_bytes.sum")})
+                               "dram_bytes_write": byts("dram__bytes_write.sum"), "lts_bytes": (g("lts__t_sectors.sum") or 0) * 32.0 or byts("lts__t_bytes.sum"),  # 32-byte sectors
+                               "l1tex_bytes": (g("SM_B.TriageCompute.l1tex__t_sectors.sum") or g("l1tex__t_sectors.sum") or 0) * 32.0 or None})
     if ent["kernels"]:
         k0 = max(ent["kernels"], key=lambda k: k["kernel_ms"])
         ent.update({k: k0[k] for k in ("kernel", "kernel_ms", "dram_bytes_read", "dram_bytes_write", "lts_bytes", "l1tex_bytes")})

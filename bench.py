@@ -398,6 +398,7 @@ def main():
     cx.dev = torch.device("cuda", local)
     gloo = None
     if world > 1:
+        os.environ["NCCL_DEBUG"] = os.environ.get("RTB_NCCL_DEBUG", "WARN")  # keep NCCL's version banner off stdout: ONE JSON line
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=cx.dev)
         gloo = dist.new_group(backend="gloo")  # host-side barrier for the rank-0-only sections (an NCCL barrier would spin on the other GPUs)

@@ -19,6 +19,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 using namespace rtb;
@@ -70,7 +71,8 @@ struct DeviceCtx {
   void* wfBlob = nullptr; size_t wfBytes = 0; WfState wf{};   // wavefront path-state slots (rt_wavefront.cuh), grown on demand
   unsigned long long* h_wfCtl = nullptr;    // pinned: {frame finished, next free path index} read back between batches of rounds
   int wfRounds = 0;                         // rounds launched for the call in flight
-  RenderArgs wfArgs{}; const void* wfScene = nullptr; int wfPrec = 0; bool wfPending = false;  // a deferred wavefrontFinish (multi-GPU shares)
+  RenderArgs wfArgs{}; const void* wfScene = nullptr; int wfPrec = 0; bool wfPending = false;  // the wavefront frame in flight
+  cudaStream_t wfStream = nullptr; cudaEvent_t wfProbe = nullptr;
   cudaStream_t stream = nullptr;            // multi-GPU shares only (the single-device entry points use the caller's / default stream)
   cudaEvent_t evStart = nullptr, evDone = nullptr;
   ~DeviceCtx() {
@@ -78,6 +80,7 @@ struct DeviceCtx {
     if (d_fb) cudaFree(d_fb);
     if (wfBlob) cudaFree(wfBlob);
     if (h_wfCtl) cudaFreeHost(h_wfCtl);
+    if (wfProbe) cudaEventDestroy(wfProbe);
     if (evStart) cudaEventDestroy(evStart);
     if (evDone) cudaEventDestroy(evDone);
     if (stream) cudaStreamDestroy(stream);
@@ -405,22 +408,49 @@ bool useWavefront(const HostScene& hs, const RtRenderParams& q, int instr) {
 }
 
 // more rounds of the wavefront until the frame-finished flag is set (blocks the host; the first batch was queued by renderLaunch)
-int wavefrontFinish(const HostScene& hs, DeviceCtx* c, const RenderArgs& a, const void* dsc, int prec, cudaStream_t st) {
+// A wavefront frame in flight on one device: batches of rounds are queued with a PROBE in their middle (a copy of {done, next free
+// path index} to pinned memory + an event), so that when the probe fires the second half of the batch is still queued and the device
+// never waits for the host.  wavefrontPoll never blocks; wavefrontFinishAll polls all the devices of a call round-robin.
+int wavefrontQueue(const HostScene& hs, DeviceCtx* c, int rounds, bool init) {
+  CU(cudaSetDevice(c->device));  // polled round-robin over the devices of a multi-GPU call
+  const int first = std::max(1, rounds / 2);
+  cudaError_t ce = launchWavefront(c->wfPrec, c->wfScene, c->wfArgs, c->wf, hs.stackDepth, c->numSMs, first, init, c->wfStream, nullptr);
+  if (ce == cudaSuccess) ce = cudaMemcpyAsync(c->h_wfCtl, c->wf.ctl + 2, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->wfStream);
+  if (ce == cudaSuccess) ce = cudaEventRecord(c->wfProbe, c->wfStream);
+  if (ce == cudaSuccess && rounds - first > 0) ce = launchWavefront(c->wfPrec, c->wfScene, c->wfArgs, c->wf, hs.stackDepth, c->numSMs, rounds - first, false, c->wfStream, nullptr);
+  if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("wavefront launch: ") + cudaGetErrorString(ce));
+  c->wfRounds += rounds;
+  return RT_OK;
+}
+// -> 1 finished, 0 still running (more rounds were queued if needed), < 0 error
+int wavefrontPoll(const HostScene& hs, DeviceCtx* c) {
+  const cudaError_t qe = cudaEventQuery(c->wfProbe);
+  if (qe == cudaErrorNotReady) return 0;
+  if (qe != cudaSuccess) return fail(RT_ERR_CUDA, std::string("wavefront probe: ") + cudaGetErrorString(qe));
+  if (c->h_wfCtl[0]) return 1;
+  const RenderArgs& a = c->wfArgs;
+  // every round finishes at least one bounce of every live path: a frame needs at most paths * (maxDepth + 1) / slots rounds plus the tail of one chunk
+  const unsigned long long bound = a.total_paths / std::max(1u, c->wf.P) * (a.maxDepth + 1ull) * 2ull + 2ull * a.wfChunk * (a.maxDepth + 2ull) + 64ull;
+  if ((unsigned long long)c->wfRounds > bound) return fail(RT_ERR_CUDA, "wavefront: the frame did not finish within its round bound (internal error)");
+  // size the next batch from the progress at the probe: rounds per handed-out path so far, then the drain of the last paths
+  const double handed = (double)std::min<unsigned long long>(c->h_wfCtl[1], a.total_paths);
+  const double frac = handed / (double)a.total_paths;
+  int more = 32;
+  if (frac > 0.02 && frac < 1.0) more = (int)std::min(2048.0, (double)c->wfRounds * (1.0 - frac) / frac * 0.6 + 16.0);
+  const int rc = wavefrontQueue(hs, c, more, false);
+  return rc ? rc : 0;
+}
+int wavefrontFinishAll(const HostScene& hs, DeviceCtx* const* ctx, int n) {
   for (;;) {
-    CU(cudaMemcpyAsync(c->h_wfCtl, c->wf.ctl + 2, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));  // done, next free path index
-    CU(cudaStreamSynchronize(st));
-    if (c->h_wfCtl[0]) return RT_OK;
-    // every round finishes at least one bounce of every live path: a frame needs at most paths * (maxDepth + 1) / slots rounds plus the tail of one chunk
-    const unsigned long long bound = a.total_paths / std::max(1u, c->wf.P) * (a.maxDepth + 1ull) * 2ull + 2ull * a.wfChunk * (a.maxDepth + 2ull) + 64ull;
-    if ((unsigned long long)c->wfRounds > bound) return fail(RT_ERR_CUDA, "wavefront: the frame did not finish within its round bound (internal error)");
-    // size the next batch from the progress so far: paths handed out per round, then the drain of the last paths
-    const double handed = (double)std::min<unsigned long long>(c->h_wfCtl[1], a.total_paths);
-    const double frac = handed / (double)a.total_paths;
-    int more = 32;
-    if (frac > 0.02 && frac < 1.0) more = (int)std::min(4096.0, (double)c->wfRounds * (1.0 - frac) / frac * 1.05 + 16.0);
-    cudaError_t ce = launchWavefront(prec, dsc, a, c->wf, hs.stackDepth, c->numSMs, more, false, st, nullptr);
-    if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("wavefront launch: ") + cudaGetErrorString(ce));
-    c->wfRounds += more;
+    bool pending = false, progressed = false;
+    for (int k = 0; k < n; ++k) {
+      if (!ctx[k]->wfPending) continue;
+      const int r = wavefrontPoll(hs, ctx[k]);
+      if (r < 0) return r;
+      if (r == 1) { ctx[k]->wfPending = false; progressed = true; } else pending = true;
+    }
+    if (!pending) return RT_OK;
+    if (!progressed) std::this_thread::yield();
   }
 }
 
@@ -485,12 +515,14 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
     const unsigned long long lanes = (unsigned long long)c->numSMs * 8ull * kBlock;
     a.chunk = (uint32_t)std::max<unsigned long long>(32, std::min<unsigned long long>(256, P / std::max<unsigned long long>(1, lanes / 32 * 4)));
     const int rounds0 = (int)std::min<unsigned long long>(4096, a.total_paths * tuneParam("RTB_WF_EST_BOUNCES", 4) / P + 24);
-    ce = launchWavefront((int)q.precision, dsc, a, c->wf, hs.stackDepth, c->numSMs, rounds0, true, st, gridOut);
-    if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("wavefront launch: ") + cudaGetErrorString(ce));
-    c->wfRounds = rounds0;
+    if (!c->wfProbe) CU(cudaEventCreateWithFlags(&c->wfProbe, cudaEventDisableTiming));
+    c->wfArgs = a; c->wfScene = dsc; c->wfPrec = (int)q.precision; c->wfStream = st; c->wfRounds = 0; c->wfPending = true;
+    if (gridOut) *gridOut = 0;
+    if ((rc = wavefrontQueue(hs, c, rounds0, true))) return rc;
     if (kindOut) *kindOut = 2u;
-    if (wfDefer) { c->wfArgs = a; c->wfScene = dsc; c->wfPrec = (int)q.precision; c->wfPending = true; return RT_OK; }
-    return wavefrontFinish(hs, c, a, dsc, (int)q.precision, st);
+    if (wfDefer) return RT_OK;  // multi-GPU shares: every device gets its first batch before any is topped up (wavefrontFinishAll)
+    DeviceCtx* one[1] = {c};
+    return wavefrontFinishAll(hs, one, 1);
   }
   if (coop && (q.flags & RT_FLAG_STRICT_MATH)) ce = launchRenderCoop<MATH_STRICT>((int)q.precision, instr, dsc, a, c->numSMs, st, gridOut);
   else if (coop) ce = launchRenderCoop<MATH_LITERAL>((int)q.precision, instr, dsc, a, c->numSMs, st, gridOut);
@@ -603,12 +635,11 @@ int renderMulti(SceneEntry* e, const RtRenderParams& q, int nGpus, double* out, 
     if ((rc = renderLaunch(e->hs, ctx[k], qk, ctx[k]->d_fb, ctx[k]->stream, 0, nullptr, nullptr, &kernelKind, /*wfDefer=*/true))) return rc;
     if (!ctx[k]->wfPending) CU(cudaEventRecord(ctx[k]->evDone, ctx[k]->stream));
   }
-  for (int k = 0; k < n; ++k) {  // wavefront shares: every device has its first batch of rounds queued; top them up until each frame is finished
-    if (!ctx[k]->wfPending) continue;
-    CU(cudaSetDevice(devs[k]));
-    if ((rc = wavefrontFinish(e->hs, ctx[k], ctx[k]->wfArgs, ctx[k]->wfScene, ctx[k]->wfPrec, ctx[k]->stream))) return rc;
-    ctx[k]->wfPending = false;
-    CU(cudaEventRecord(ctx[k]->evDone, ctx[k]->stream));
+  {  // wavefront shares: every device has its first batch of rounds queued; top them up round-robin until each frame is finished
+    std::vector<int> wasPending(n);
+    for (int k = 0; k < n; ++k) wasPending[k] = ctx[k]->wfPending ? 1 : 0;
+    if ((rc = wavefrontFinishAll(e->hs, ctx.data(), n))) return rc;
+    for (int k = 0; k < n; ++k) if (wasPending[k]) { CU(cudaSetDevice(devs[k])); CU(cudaEventRecord(ctx[k]->evDone, ctx[k]->stream)); }
   }
   // reduction onto the root
   CU(cudaSetDevice(root->device));

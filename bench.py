@@ -431,7 +431,8 @@ def main():
                     ("cfg4", "cornell", 1000, small, 2, 1000, None), ("cfg5_90k", "synthetic", 1, 2, 1, 300, (480, 270)),
                     ("cfg5_1m", "synthetic", 1, 1, 1, 1000, (240, 135))]
         else:
-            plan = [("cfg3", "next_week_final", 256, 2, 1, 1000, None), ("cfg4", "cornell", 1000, 2, 1, 1000, None)]
+            plan = [("cfg3", "next_week_final", 256, 2, 1, 1000, None), ("cfg4", "cornell", 1000, 2, 1, 1000, None),
+                    ("cfg5_1m", "synthetic", 1, 1, 1, 1000, (240, 135))]
         for key, sc, s, st, wu, sn, size in plan:
             r = measure(cx, sc, s, st, wu, synth_n=sn, size=size)
             if rank == 0:

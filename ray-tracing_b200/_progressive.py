@@ -16,7 +16,7 @@ _KEYS = ("width", "height", "total_spp", "depth", "seed", "precision", "flags", 
 
 
 class ProgressiveRender:
-    def __init__(self, scene, width, height, total_spp, depth=50, seed=1, precision=0, flags=0, tag=""):
+    def __init__(self, scene, width, height, total_spp, depth=50, seed=1, precision=1, flags=0, tag=""):  # precision 1 = RT_PREC_DEFAULT (mixed)
         """`scene`: a DeviceScene (anything with render(W, H, spp, depth=, seed=, s0=, precision=, flags=, total=) -> (sums, stats)).
         `tag`: free text naming the scene; stored in checkpoints and compared on resume."""
         if width <= 0 or height <= 0 or total_spp < 0:

@@ -146,7 +146,7 @@ def test_render_matches_oracle_same_streams(gpu, O, oracle_scene, dev_scene, nam
     gp, op = {"f32": (gpu.PREC_F32, O.PREC_F32), "mixed": (gpu.PREC_MIXED, O.PREC_MIXED)}[prec]
     img, st = dev_scene(name, lit).render(W, H, spp, depth=50, seed=21, precision=gp)
     ref, _ = oracle_scene(name, lit).render(W, H, spp, depth=50, prec=op, mode=1, seed=21)
-    assert st["samples"] == W * H * spp and st["launches"] == 1
+    assert st["samples"] == W * H * spp and st["launches"] >= 1  # 1 for renderKernel; the wavefront path launches two kernels per round
     media = name in ("cornell_smoke", "next_week_final")
     _cmp_images(img, ref, frac_min=0.80 if media else 0.90, mean_tol=0.04 if media else 0.02)
 

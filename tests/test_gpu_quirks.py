@@ -83,9 +83,15 @@ def test_quirks_render_fp64(gpu, O, oracle_scene, quirks):
     ng, nr = np.isnan(img).any(axis=2), np.isnan(ref).any(axis=2)
     assert np.array_equal(ng, nr)
     rel = (np.abs(img[~ng] - ref[~ng]) / (np.abs(ref[~ng]) + 1e-3)).max(axis=1)
-    # the nested light-list weights multiply in another order on the device (1e-16 per product), and the scene's fuzz-2 metal and
-    # glass chains amplify that: observed 99.9 % within 1e-12, all within 1e-6 (profiles/r2_parity_fractions.json)
-    assert (rel < 1e-9).mean() >= 0.99 and (rel < 1e-6).mean() >= 0.999, (float((rel < 1e-9).mean()), float(rel.max()))
+    # default math: CUDA's and glibc's log / sin / cos / atan2 differ in the last ulp, which separates a handful of the 9600 paths at
+    # a medium's free-flight comparison or a t_min self-hit (observed on B200: 5-6 of 2400 pixels, profiles/r2_parity_classification.json);
+    # every other pixel agrees to double round-off.  Under RT_FLAG_STRICT_MATH the same scene is held to 1e-12 (test_gpu_strict.py).
+    assert (rel < 1e-9).mean() >= 0.99, (float((rel < 1e-9).mean()), float(rel.max()))
+    simg, _ = quirks(True).render(W, H, 4, depth=50, seed=33, precision=gpu.PREC_F64, flags=gpu.FLAG_STRICT_MATH)
+    sref, _ = oracle_scene("quirks", True).render(W, H, 4, depth=50, prec=O.PREC_F64, mode=1, seed=33, strict=True, order="beta")
+    assert np.array_equal(np.isnan(simg), np.isnan(sref))
+    ok = ~np.isnan(sref)
+    assert np.isclose(simg[ok], sref[ok], rtol=1e-12, atol=1e-12).mean() >= 0.999
 
 
 def test_quirks_counters(gpu, O, oracle_scene, quirks):

@@ -20,7 +20,7 @@ RTB_WAVEFRONT=0 cap cornell_renderKernel_spp32 cornell 32 "" "" renderKernel 3
 cap cornell_wfTraverse_spp64 cornell 64 "" "" wfTraverseKernel 150
 cap cornell_wfShade_spp64 cornell 64 "" "" wfShadeKernel 150
 cap synthetic300_coop synthetic 1 300 480x270 renderKernelCoop 2
-cap synthetic1000_coop synthetic 1 1000 120x68 renderKernelCoop 2
+cap synthetic1000_coop synthetic 1 1000 240x135 renderKernelCoop 2
 timeout 200 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/${tag}_launches_cornell_spp64.csv \
     python bench.py --scene cornell --spp 64 --steps 1 --warmup 1 --profile > gpurun_out/${tag}_ncu_launches_cornell.log 2>&1; echo "cornell launch list rc=$?"
 # summaries and the traffic table are made here, the reports themselves (8-14 MB each) stay on the box: gpurun_out/ is capped at 64 MiB
@@ -28,6 +28,6 @@ for f in gpurun_out/${tag}_*.ncu-rep; do python tools/ncu_summary.py $f 64 > ${f
 python tools/make_traffic.py gpurun_out/${tag}_traffic.json next_week_final_spp16=400,400,16,gpurun_out/${tag}_next_week_final_spp16.ncu-rep \
   cornell_renderKernel_spp32=500,500,32,gpurun_out/${tag}_cornell_renderKernel_spp32.ncu-rep cornell_wfTraverse_round=500,500,64,gpurun_out/${tag}_cornell_wfTraverse_spp64.ncu-rep \
   cornell_wfShade_round=500,500,64,gpurun_out/${tag}_cornell_wfShade_spp64.ncu-rep synthetic_300=480,270,1,gpurun_out/${tag}_synthetic300_coop.ncu-rep \
-  synthetic_1000_120x68=120,68,1,gpurun_out/${tag}_synthetic1000_coop.ncu-rep > gpurun_out/${tag}_traffic.log 2>&1
+  synthetic_1000=240,135,1,gpurun_out/${tag}_synthetic1000_coop.ncu-rep > gpurun_out/${tag}_traffic.log 2>&1
 rm -f gpurun_out/${tag}_*.ncu-rep
 ls -la gpurun_out/ | grep ${tag}

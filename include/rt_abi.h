@@ -258,6 +258,26 @@ int rt_render(rt_scene_t scene, const RtRenderParams* params, double* out_rgb_su
  * framebuffers with NCCL without host staging. */
 int rt_render_device(rt_scene_t scene, const RtRenderParams* params, double* d_out_rgb_sum, void* cuda_stream, RtStats* stats);
 
+/* NO COUNTERPART IN THE REFERENCE — added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  rt_render's contract with a DEVICE output buffer and
+ * NO allocation: renderKernel's scratch — its work-counter block and the double framebuffer it accumulates into — lives in a
+ * static __device__ array of the library, RT_STATIC_MAX_PIXELS * 24 + 512 bytes = 6 MiB + 512 B, held by every GPU that loads the
+ * library until the process exits.  The call clears the part of the scratch it uses, launches renderKernel on `cuda_stream`
+ * (cudaStream_t as void*, NULL = default stream), then copies the rendered region onto d_out_rgb_sum (double[height*width*3] on
+ * the scene's device; the region is OVERWRITTEN, other pixels are left untouched) on the same stream, and returns without
+ * synchronising.  It calls no cudaMalloc / cudaFree / event or stream creation.
+ *   - width*height > RT_STATIC_MAX_PIXELS  -> RT_ERR_UNSUPPORTED (message names both numbers); use rt_render_device.
+ *   - renderKernel only: RT_FLAG_COOP / RT_FLAG_WAVEFRONT / n_gpus > 1 -> RT_ERR_UNSUPPORTED.
+ *   - the scene must already be on the device in the requested arithmetic (rt_scene_create uploads fp32 / mixed; the first fp64
+ *     call of another entry point uploads fp64), else RT_ERR_UNSUPPORTED.
+ *   - ALL calls on one GPU share the one array (whatever the scene handle) and it keeps the last call's contents: calls whose
+ *     GPU work overlaps (different streams, or another thread before the first call's stream work has finished) RACE.  Issue them
+ *     on one stream, or order the streams with events.
+ *   - the first call on a device resolves the array's device address (cudaGetSymbolAddress; may load the module): make one
+ *     warm-up call outside graph capture. */
+#define RT_STATIC_MAX_PIXELS 262144u /* 512 x 512: covers the reference's 600x400 and 500x500 frames */
+int rt_render_device_static(rt_scene_t scene, const RtRenderParams* params, double* d_out_rgb_sum, void* cuda_stream);
+
 /* Same as rt_render with the algorithmic-work counters of RtStats filled (slower instrumented kernel). */
 int rt_render_counted(rt_scene_t scene, const RtRenderParams* params, double* out_rgb_sum, RtStats* stats);
 

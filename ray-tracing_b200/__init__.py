@@ -23,6 +23,7 @@ FLAG_COOP = 4
 FLAG_NO_COOP = 8
 FLAG_WAVEFRONT = 16
 FLAG_NO_WAVEFRONT = 32
+STATIC_MAX_PIXELS = 262144  # RT_STATIC_MAX_PIXELS (rt_render_device_static)
 INIT_NCCL = 1
 REDUCE_KINDS = ["none", "peer-kernel", "nccl", "staged"]
 RT_NONE = 0xFFFFFFFF
@@ -76,7 +77,7 @@ class RtLimits(C.Structure):
 
 
 ABI_SYMBOLS = ["rt_abi_version", "rt_last_error", "rt_device_count", "rt_get_limits", "rt_init", "rt_scene_create", "rt_scene_destroy",
-               "rt_render", "rt_render_device", "rt_render_counted", "rt_render_pathlog", "rt_trace", "rt_texture_value", "rt_tonemap",
+               "rt_render", "rt_render_device", "rt_render_device_static", "rt_render_counted", "rt_render_pathlog", "rt_trace", "rt_texture_value", "rt_tonemap",
                "rt_selftest_division", "rt_strict_math_eval", "rt_bvh_node_count", "rt_bvh_build", "rt_shutdown"]
 
 _core = None
@@ -105,6 +106,7 @@ def core():
         for f in (L.rt_render, L.rt_render_counted):
             f.argtypes = [C.c_uint64, C.POINTER(RtRenderParams), C.c_void_p, C.POINTER(RtStats)]
         L.rt_render_device.argtypes = [C.c_uint64, C.POINTER(RtRenderParams), C.c_void_p, C.c_void_p, C.POINTER(RtStats)]
+        L.rt_render_device_static.argtypes = [C.c_uint64, C.POINTER(RtRenderParams), C.c_void_p, C.c_void_p]
         L.rt_trace.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_double, C.c_double, C.c_uint64,
                                C.c_uint32] + [C.c_void_p] * 8
         L.rt_texture_value.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]

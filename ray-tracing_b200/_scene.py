@@ -128,6 +128,11 @@ class DeviceScene:
         _check(core().rt_render_device(self.id, C.byref(p), C.c_void_p(d_ptr), C.c_void_p(stream), C.byref(st) if timed else None))
         return dict(kernel_ms=st.kernel_ms, launches=int(st.launches), rounds=int(st.rounds), kernel=["renderKernel", "renderKernelCoop", "wavefront"][st.kernel_kind]) if timed else None
 
+    def render_device_static(self, d_ptr, W, H, spp, stream=0, **kw):
+        """rt_render_device_static: no allocation, scratch in the library's static device array (include/rt_abi.h); asynchronous on `stream`"""
+        p = self.params(W, H, spp, **kw)
+        _check(core().rt_render_device_static(self.id, C.byref(p), C.c_void_p(d_ptr), C.c_void_p(stream)))
+
     def render_pathlog(self, W, H, spp, max_bounces=50, **kw):
         """-> (radiance sums, prim_log uint32 [paths, max_bounces] (0xfffffffe = bounce not reached, 0xffffffff = miss), t_log float64)"""
         p = self.params(W, H, spp, **kw)

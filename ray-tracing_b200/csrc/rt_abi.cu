@@ -792,6 +792,31 @@ int renderHost(rt_scene_t scene, const RtRenderParams* params, double* out, RtSt
   return RT_OK;
 }
 
+// ---- rt_render_device_static: renderKernel's scratch (the work-counter block and the double framebuffer the kernel accumulates into)
+// in a STATIC device array instead of cudaMalloc'd buffers, for callers that may not allocate (include/rt_abi.h).  No counterpart in
+// the reference.  Every GPU that loads the library holds the array until exit.
+constexpr size_t kStaticCtrWords = 64;                                   // >= kCtrTotal, keeps the framebuffer 256-byte aligned
+constexpr size_t kStaticFbElems = (size_t)RT_STATIC_MAX_PIXELS * 3;      // doubles
+static_assert(kCtrTotal <= (int)kStaticCtrWords, "counter block does not fit the static scratch");
+static __device__ __align__(256) unsigned long long g_staticScratch[kStaticCtrWords + kStaticFbElems];  // 8-byte words: counters, then the framebuffer
+
+std::mutex g_staticMu;                           // host side of the calls is serialised; launches that overlap on the GPU still race (documented)
+unsigned long long* g_staticPtr[64] = {};        // per device: the array's DEVICE address (the symbol itself is only a host-side stand-in)
+
+// once per device, with that device current
+int staticScratch(int device, unsigned long long** out) {
+  if (device < 0 || device >= 64) return fail(RT_ERR_ARG, "rt_render_device_static: device index out of range");
+  if (!g_staticPtr[device]) {
+    CU(cudaSetDevice(device));
+    void* p = nullptr;
+    cudaError_t ce = cudaGetSymbolAddress(&p, g_staticScratch);
+    if (ce != cudaSuccess || !p) return fail(RT_ERR_CUDA, std::string("cudaGetSymbolAddress(static scratch): ") + cudaGetErrorString(ce));
+    g_staticPtr[device] = static_cast<unsigned long long*>(p);
+  }
+  *out = g_staticPtr[device];
+  return RT_OK;
+}
+
 }  // namespace
 
 namespace rtb { void setLastError(const std::string& s) { g_err = s; } }  // for the other translation units of the library
@@ -1047,6 +1072,67 @@ int rt_render_device(rt_scene_t scene, const RtRenderParams* params, double* d_o
     stats->gpus = 1; stats->gpu_kernel_ms[0] = ms; stats->kernel_kind = kernelKind;
     if (kernelKind == 2) { stats->rounds = (uint32_t)e->main.wfRounds; stats->launches = 1ull + 2ull * (uint64_t)e->main.wfRounds; }
   }
+  return RT_OK;
+}
+
+// No cudaMalloc / cudaFree / event creation on this path: memsets, one renderKernel launch and one 2-D device copy, all on the
+// caller's stream.  The device copy of the scene in the requested arithmetic must already exist (rt_scene_create uploads fp32 /
+// mixed; fp64 is uploaded by the first fp64 call of another entry point).
+int rt_render_device_static(rt_scene_t scene, const RtRenderParams* params, double* d_out, void* cuda_stream) {
+  const std::shared_ptr<SceneEntry> ep = lookup(scene);
+  if (!ep) return fail(RT_ERR_HANDLE, "unknown scene handle");
+  SceneEntry* e = ep.get();
+  std::lock_guard<std::mutex> lk(e->mu);
+  if (!d_out) return fail(RT_ERR_ARG, "d_out_rgb_sum is null");
+  RtRenderParams q;
+  int rc = normaliseParams(params, q);
+  if (rc) return rc;
+  if ((uint64_t)q.width * q.height > RT_STATIC_MAX_PIXELS)
+    return fail(RT_ERR_UNSUPPORTED, "rt_render_device_static: width*height = " + std::to_string((uint64_t)q.width * q.height) + " pixels exceeds RT_STATIC_MAX_PIXELS = " +
+                                        std::to_string((uint64_t)RT_STATIC_MAX_PIXELS) + " (the static scratch framebuffer); use rt_render_device");
+  if (q.flags & (RT_FLAG_COOP | RT_FLAG_WAVEFRONT)) return fail(RT_ERR_UNSUPPORTED, "rt_render_device_static runs renderKernel only (no RT_FLAG_COOP / RT_FLAG_WAVEFRONT)");
+  if (q.n_gpus > 1) return fail(RT_ERR_UNSUPPORTED, "rt_render_device_static renders on the scene's device only");
+  DeviceCtx* c = &e->main;
+  const void* dsc = nullptr;
+  if (q.precision == RT_PREC_F64) { if (c->f64.ready) dsc = &c->f64.sc; }
+  else if (c->f32.ready) dsc = &c->f32.sc;
+  if (!dsc) return fail(RT_ERR_UNSUPPORTED, "rt_render_device_static: the scene is not on the device in this arithmetic yet (uploading allocates): render it once through rt_render / rt_render_device first");
+  std::lock_guard<std::mutex> lk2(g_staticMu);
+  CU(cudaSetDevice(c->device));
+  unsigned long long* scratch = nullptr;
+  if ((rc = staticScratch(c->device, &scratch))) return rc;
+  double* fb = reinterpret_cast<double*>(scratch + kStaticCtrWords);
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  const size_t rowElems = (size_t)q.width * 3;
+  // the array keeps the last call's contents: the counter block and the rows this call accumulates into start at zero
+  CU(cudaMemsetAsync(scratch, 0, kStaticCtrWords * sizeof(unsigned long long), st));
+  CU(cudaMemsetAsync(fb + q.row0 * rowElems, 0, (size_t)(q.row1 - q.row0) * rowElems * sizeof(double), st));
+  if (q.sample_count) {
+    const HostScene& hs = e->hs;
+    RenderArgs a{};  // the same launch parameters as renderLaunch's renderKernel branch (results never depend on the scheduler knobs)
+    a.W = q.width; a.H = q.height; a.s0 = q.sample_offset; a.ns = q.sample_count; a.maxDepth = q.max_depth;
+    a.row0 = q.row0; a.row1 = q.row1; a.col0 = q.col0; a.col1 = q.col1;
+    a.seed = q.seed;
+    a.total_paths = (unsigned long long)(q.row1 - q.row0) * (q.col1 - q.col0) * q.sample_count;
+    const unsigned long long warps = (unsigned long long)c->numSMs * 16ull;
+    unsigned long long chunk = 1024;
+    while (chunk > 4 && a.total_paths / chunk < warps * 8ull) chunk /= 2;
+    a.chunk = (uint32_t)chunk;
+    a.chunkMin = (uint32_t)std::min<unsigned long long>(chunk, 32);
+    a.chunkDiv = (uint32_t)std::max<unsigned long long>(1, warps * 2);
+    a.shadeMin = 16; a.rectMin = hs.n_cuboids > hs.n_rects ? 6u : 3u; a.rareMin = hs.n_media > 0 ? 4u : 8u; a.keepNode = 12; a.keepLeaf = 8;
+    a.lightCap = hs.lightCap;
+    a.counter = scratch; a.ctr = nullptr; a.out = fb;
+    cudaError_t ce;
+    if (q.flags & RT_FLAG_FAST_MATH) ce = launchRender<MATH_FAST>((int)q.precision, 0, dsc, a, hs.stackDepth, c->numSMs, st, nullptr);
+    else if (q.flags & RT_FLAG_STRICT_MATH) ce = launchRender<MATH_STRICT>((int)q.precision, 0, dsc, a, hs.stackDepth, c->numSMs, st, nullptr);
+    else ce = launchRender<MATH_LITERAL>((int)q.precision, 0, dsc, a, hs.stackDepth, c->numSMs, st, nullptr);
+    if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("render launch: ") + cudaGetErrorString(ce));
+  }
+  // rt_render's contract on a device buffer: the rendered region is OVERWRITTEN with this call's sums, other pixels stay untouched
+  const size_t off = q.row0 * rowElems + (size_t)q.col0 * 3;
+  CU(cudaMemcpy2DAsync(d_out + off, rowElems * sizeof(double), fb + off, rowElems * sizeof(double), (size_t)(q.col1 - q.col0) * 3 * sizeof(double), q.row1 - q.row0,
+                       cudaMemcpyDeviceToDevice, st));
   return RT_OK;
 }
 

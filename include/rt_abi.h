@@ -313,6 +313,13 @@ int rt_tonemap(const double* rgb_sum, uint32_t n, uint32_t total_samples, uint8_
  * *mismatches == 0.  Not part of the reference path. */
 int rt_selftest_division(uint64_t n, uint64_t seed, uint64_t* checked, uint64_t* mismatches);
 
+/* Device self-test of the interval filter in front of that division (slabFiltered, rt_device.cuh: boxRayIntersect, Lib.hs:798-814,
+ * decided from one-instruction approximate quotients whenever the comparison margin exceeds their error bound): n random and
+ * adversarial (box, ray, [t_min, t_max]) triples; out3 = {triples checked, of those decided by the filter alone, filter decisions
+ * that differ from the decision of the three IEEE divisions}.  Bit-exact traversal requires out3[2] == 0.  Not part of the
+ * reference path. */
+int rt_selftest_box_filter(uint64_t n, uint64_t seed, uint64_t out3[3]);
+
 /* makeBVH (Lib.hs:941-961) built on the device, tree-identical to the host recursion: the node's objects are sorted stably by
  * box_min[axis] (Data.Sequence.sortBy of boxCompare, Lib.hs:963-968), split at n `div` 2; one object -> BVHNode h h (948),
  * two objects -> ordered by `comparator h1 h2 == LT`, ties swapped (949-952); box = surroundingBox of the children (929-939).

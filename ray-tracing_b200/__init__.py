@@ -78,7 +78,7 @@ class RtLimits(C.Structure):
 
 ABI_SYMBOLS = ["rt_abi_version", "rt_last_error", "rt_device_count", "rt_get_limits", "rt_init", "rt_scene_create", "rt_scene_destroy",
                "rt_render", "rt_render_device", "rt_render_device_static", "rt_render_counted", "rt_render_pathlog", "rt_trace", "rt_texture_value", "rt_tonemap",
-               "rt_selftest_division", "rt_strict_math_eval", "rt_bvh_node_count", "rt_bvh_build", "rt_shutdown"]
+               "rt_selftest_division", "rt_selftest_box_filter", "rt_strict_math_eval", "rt_bvh_node_count", "rt_bvh_build", "rt_shutdown"]
 
 _core = None
 _host = None
@@ -111,6 +111,7 @@ def core():
                                C.c_uint32] + [C.c_void_p] * 8
         L.rt_texture_value.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
         L.rt_init.argtypes = [C.c_int, C.c_uint32]
+        L.rt_selftest_box_filter.argtypes = [C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]
         L.rt_render_pathlog.argtypes = [C.c_uint64, C.POINTER(RtRenderParams), C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
         L.rt_strict_math_eval.argtypes = [C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.rt_tonemap.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]

@@ -334,6 +334,8 @@ template <class T> int buildDevice(const HostScene& h, DevBuffers<T>& db) {
   sc.world_root = h.world_root; sc.lights_root = h.lights_root;
   sc.bigCoords = 0; sc.pad_ = 0;
   for (double v : h.node_box) if (!(std::fabs(v) <= 1099511627776.0)) sc.bigCoords = 1;  // beyond 2^40 or non-finite (rt_device.cuh kDivHi)
+  for (double v : h.rect) if (!(std::fabs(v) <= 1099511627776.0)) sc.bigCoords = 1;      // plane quotients use the same hoisted reciprocal (rectTHoisted)
+  for (double v : h.cuboid) if (!(std::fabs(v) <= 1099511627776.0)) sc.bigCoords = 1;
   for (int i = 0; i < 3; ++i) sc.bg[i] = (T)h.background[i];
   for (int i = 0; i < 24; ++i) sc.cam[i] = (T)h.camera[i];
   db.ready = true;
@@ -1230,6 +1232,22 @@ int rt_selftest_division(uint64_t n, uint64_t seed, uint64_t* checked, uint64_t*
   cudaFree(d);
   if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("division selftest: ") + cudaGetErrorString(ce));
   *checked = h[0]; *mismatches = h[1];
+  return RT_OK;
+}
+
+int rt_selftest_box_filter(uint64_t n, uint64_t seed, uint64_t out3[3]) {
+  if (!out3) return fail(RT_ERR_ARG, "null output");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(RT_ERR_CUDA, "no CUDA device available (this library has no CPU path)"); }
+  unsigned long long* d = nullptr;
+  CU(cudaMalloc(&d, 3 * sizeof(unsigned long long)));
+  CU(cudaMemset(d, 0, 3 * sizeof(unsigned long long)));
+  cudaError_t ce = launchBoxFilterSelftest(n, seed, d, 0);
+  unsigned long long h[3] = {0, 0, 0};
+  if (ce == cudaSuccess) ce = cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  if (ce != cudaSuccess) return fail(RT_ERR_CUDA, std::string("box filter selftest: ") + cudaGetErrorString(ce));
+  out3[0] = h[0]; out3[1] = h[1]; out3[2] = h[2];
   return RT_OK;
 }
 

@@ -64,6 +64,7 @@ template <int MODE> cudaError_t launchTraceCoop(int prec, const void* dscene, co
 template <int MODE> cudaError_t launchTexture(int prec, const void* dscene, uint32_t tex, uint32_t n, const double* q, double* out, cudaStream_t st);
 cudaError_t launchStrictMathEval(uint32_t fn, uint32_t n, const double* x, const double* y, double* out, int as_float, cudaStream_t st);
 cudaError_t launchDivSelftest(unsigned long long n, unsigned long long seed, unsigned long long* out2, cudaStream_t st);
+cudaError_t launchBoxFilterSelftest(unsigned long long n, unsigned long long seed, unsigned long long* out3, cudaStream_t st);
 // dst[i] += src[0][i] + ... + src[n-1][i] (left to right), src may be peer-device memory (NVLink loads)
 cudaError_t launchReducePeer(double* dst, const double* const* src, int n, size_t elems, int numSMs, cudaStream_t st);
 cudaError_t launchTonemap(const double* sum, uint32_t n, double ns, uint8_t* out, cudaStream_t st);

@@ -38,6 +38,63 @@ cudaError_t launchDivSelftest(unsigned long long n, unsigned long long seed, uns
   return cudaGetLastError();
 }
 
+// Decision equality of the interval-filtered slab test (slabFiltered, rt_device.cuh) with boxRayIntersect evaluated by three IEEE
+// divisions (Lib.hs:798-814), over random (box, ray, interval) triples: a third generic (ray through / past a random box), two thirds
+// adversarial -- a box face placed so that its quotient lands within 32 ulps of t_min or t_max, boxes a few ulps thin (a Rect's
+// bounding box at Cornell scale), near-zero numerators.  out3 = {triples in the hoisted-reciprocal range, of those decided by the
+// filter alone, filter decisions that differ from the IEEE decision}.  The last must be 0.
+static __global__ void boxFilterSelftestKernel(unsigned long long n, unsigned long long seed, unsigned long long* out3) {
+  const unsigned long long tid = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x, nthreads = (unsigned long long)gridDim.x * blockDim.x;
+  Rng g = streamGen(seed, (uint32_t)tid, (uint32_t)(tid >> 32));
+  unsigned long long checked = 0, decided = 0, bad = 0;
+  auto unit = [&]() { return (float)(nextWord(g) >> 40) * (1.0f / 16777216.0f); };                      // [0, 1)
+  auto nudge = [&](float x, int k) { return __uint_as_float(__float_as_uint(x) + (uint32_t)k); };        // k ulps away from zero / towards it
+  for (unsigned long long i = tid; i < n; i += nthreads) {
+    const unsigned long long w = nextWord(g);
+    const float scale = __uint_as_float((uint32_t)(120u + (w & 15u)) << 23);                              // 2^-7 .. 2^8
+    float o[3], d[3], lo[3], hi[3];
+    for (int k = 0; k < 3; ++k) {
+      o[k] = (unit() - 0.5f) * 2.0f * scale;
+      const float mag = __uint_as_float((uint32_t)(112u + ((w >> (8 + 5 * k)) & 15u)) << 23);             // 2^-15 .. 2^0
+      d[k] = (unit() + 0.5f) * mag * (((w >> (4 + k)) & 1u) ? -1.0f : 1.0f);
+    }
+    const float tstar = unit() * 4.0f * scale + 1e-3f;
+    float t_min = ((w >> 24) & 1u) ? 1e-4f : 0.0f, t_max = ((w >> 25) & 3u) ? tstar * (0.25f + 2.0f * unit()) : __int_as_float(0x7f800000);
+    for (int k = 0; k < 3; ++k) {
+      const float c = o[k] + d[k] * tstar * (0.5f + unit()), e = unit() * 0.25f * scale;
+      lo[k] = c - e; hi[k] = c + e;
+    }
+    const uint32_t kind = (uint32_t)((w >> 28) % 6u), ax = (uint32_t)((w >> 32) % 3u);
+    const int ulps = (int)((w >> 36) & 63u) - 32;  // +-32 ulps = +-3.8e-6 relative: both sides of the filter's threshold
+    if (kind == 1u) { const float q = __fdiv_rn(lo[ax] - o[ax], d[ax]); if (q > 0.0f) t_max = nudge(q, ulps); }          // near face at t_max
+    else if (kind == 2u) { const float q = __fdiv_rn(hi[ax] - o[ax], d[ax]); if (q > 0.0f) t_min = nudge(q, ulps); }     // far face at t_min
+    else if (kind == 3u) hi[ax] = nudge(lo[ax], (int)((w >> 36) & 7u));                                                   // 0 .. 7 ulps thin
+    else if (kind == 4u) { lo[ax] = o[ax]; if ((w >> 40) & 1u) hi[ax] = nudge(o[ax], 1 + (int)((w >> 36) & 3u)); }          // exact-zero numerator
+    else if (kind == 5u) { const float q = __fdiv_rn(hi[ax] - o[ax], d[ax]); if (q > 0.0f) t_max = nudge(q, ulps); }     // far face at t_max
+    if (hi[ax] < lo[ax]) { const float t = lo[ax]; lo[ax] = hi[ax]; hi[ax] = t; }
+    // a quarter of the triples have one or two zero direction components (the reference's (1, 0, 0) light direction): division mode 1
+    if (((w >> 44) & 3u) == 0u) { d[(ax + 1u) % 3u] = ((w >> 46) & 1u) ? -0.0f : 0.0f; if ((w >> 47) & 1u) d[(ax + 2u) % 3u] = 0.0f; }
+    if (kind == 4u && ((w >> 48) & 1u)) lo[(ax + 1u) % 3u] = o[(ax + 1u) % 3u];   // 0 * inf = NaN on a zero-divisor axis
+    for (int k = 0; k < 3; ++k) if (hi[k] < lo[k]) { const float t = lo[k]; lo[k] = hi[k]; hi[k] = t; }
+    bool ok = true;
+    float rr[3];
+    for (int k = 0; k < 3; ++k) { uint32_t mode; axisMode(d[k], true, rr[k], mode); ok = ok && mode != 2u; }
+    if (!ok) continue;
+    ++checked;
+    bool sure = true, pass = true, ref = true;
+    for (int k = 0; k < 3; ++k) {
+      pass = slabFiltered(lo[k], hi[k], o[k], rr[k], t_min, fminf(t_max, 3.4028234663852886e38f), sure) && pass;  // as stepNode calls it
+      ref = slabDecide<float>(__fdiv_rn(lo[k] - o[k], d[k]), __fdiv_rn(hi[k] - o[k], d[k]), t_min, t_max) && ref;
+    }
+    if (sure) { ++decided; if (pass != ref) ++bad; }
+  }
+  atomicAdd(out3, checked); atomicAdd(out3 + 1, decided); atomicAdd(out3 + 2, bad);
+}
+cudaError_t launchBoxFilterSelftest(unsigned long long n, unsigned long long seed, unsigned long long* out3, cudaStream_t st) {
+  boxFilterSelftestKernel<<<148 * 8, 256, 0, st>>>(n, seed, out3);
+  return cudaGetLastError();
+}
+
 // ---- wavefront launcher (literal arithmetic only)
 size_t wfLayout(uint32_t P, char* base, WfState* out) {
   size_t off = 0;

@@ -240,7 +240,7 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
     } else if (pick == 1) {
       if (isLeaf) stepSphere<T, S, INSTR>(sc, tr, (ps.phase == PH_MAIN) ? ps.time : (T)0, ins);  // htblPdfValue traces with time 0 (Lib.hs:677)
     } else if (pick == 2) {
-      if (cls == 2) stepRect<T, INSTR>(sc, tr, ins);
+      if (cls == 2) stepRect<T, INSTR, MODE>(sc, tr, ins);
     } else if (pick == 3) {
       if (cls == 3) stepRare<T, INSTR, MODE>(sc, tr, ps.rng, ins);
     }

@@ -140,6 +140,28 @@ RTB_D void stepNode(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
   bool pass;
   if constexpr (MODE != MATH_FAST && sizeof(T) == 4) {
     bool ok = (tr.flags & F_MODE_GENERIC) == 0u;  // no axis in the generic division mode
+    if constexpr (kSlabFilter) {
+      // interval filter: the approximate quotients decide unless a comparison margin is inside their error bound (rt_device.cuh)
+      bool sure = ok;  // no axis in the generic division mode; zero divisors are handled by the filter itself
+      // t_max = +inf (no hit yet) enters as FLT_MAX: same decisions (finite quotients are < 2^81, infinite ones compare alike), and a
+      // zero-divisor axis that misses the box (both quotients +inf) gives m = -inf, a certain "no", instead of inf - inf
+      const float tF = fminf(tr.tbest, 3.4028234663852886e38f);
+      const bool fx = slabFiltered(lo.x, hi.x, tr.o.x, tr.inv.x, tr.tmin, tF, sure);
+      const bool fy = slabFiltered(lo.y, hi.y, tr.o.y, tr.inv.y, tr.tmin, tF, sure);
+      const bool fz = slabFiltered(lo.z, hi.z, tr.o.z, tr.inv.z, tr.tmin, tF, sure);
+#ifdef RTB_DEBUG_UNSURE
+      if (!sure) ins.count(23);
+      if ((tr.flags & F_MODE_MASK) != 0u) ins.count(22);
+#endif
+      if (sure) {
+        if (fx & fy & fz) descend(); else tr.next();
+        return;
+      }
+      if (boxRefined(lo.x, lo.y, lo.z, hi.x, hi.y, hi.z, tr.o.x, tr.o.y, tr.o.z, tr.d.x, tr.d.y, tr.d.z, tr.inv.x, tr.inv.y, tr.inv.z,
+                     (tr.flags & F_MODE_GENERIC) != 0u, tr.tmin, tr.tbest)) descend();
+      else tr.next();
+      return;
+    }
     const bool bx = slabHoisted(lo.x, hi.x, tr.o.x, tr.d.x, tr.inv.x, tr.tmin, tr.tbest, ok);
     const bool by = slabHoisted(lo.y, hi.y, tr.o.y, tr.d.y, tr.inv.y, tr.tmin, tr.tbest, ok);
     const bool bz = slabHoisted(lo.z, hi.z, tr.o.z, tr.d.z, tr.inv.z, tr.tmin, tr.tbest, ok);
@@ -190,8 +212,13 @@ RTB_D void stepSphere(const DScene<T>& sc, Trav<T>& tr, T time, Instr<INSTR>& in
 }
 
 // Rect and Cuboid leaves
-template <class T, int INSTR>
+template <class T, int INSTR, int MODE = MATH_LITERAL>
 RTB_D void stepRect(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
+  // plane quotients through the ray's refined reciprocal in the fp32 literal / strict builds (rt_device.cuh rectTHoisted)
+  auto rectHit = [&](uint32_t plane, T i0, T i1, T j0, T j1, T k, T& t) -> bool {
+    if constexpr (MODE != MATH_FAST && sizeof(T) == 4 && kPlaneHoist && kRectHoist) return rectTHoisted(plane, i0, i1, j0, j1, k, tr.o, tr.d, tr.inv, tr.flags >> F_MODE_SHIFT, tr.tmin, tr.tbest, t);
+    else return rectT<T>(plane, i0, i1, j0, j1, k, tr.o, tr.d, tr.tmin, tr.tbest, t);
+  };
   uint32_t ref = tr.cur, ref2 = kNone;
   if (ref & kPairBit) {  // the two leaves of a bottom node, left then right
     const uint32_t n = ref & kIdxMask;
@@ -204,18 +231,15 @@ RTB_D void stepRect(const DScene<T>& sc, Trav<T>& tr, Instr<INSTR>& ins) {
     if (kind != K_CUBOID) {
       const Q4<T> a = ldq(sc.rects + 2 * (size_t)idx), b = ldq(sc.rects + 2 * (size_t)idx + 1);
       T t;
-      if (rectT<T>(kind - K_RECT_XY, a.x, a.y, a.z, a.w, b.x, tr.o, tr.d, tr.tmin, tr.tbest, t)) travAccept<T>(tr, t, ref, 0);
+      if (rectHit(kind - K_RECT_XY, a.x, a.y, a.z, a.w, b.x, t)) travAccept<T>(tr, t, ref, 0);
     } else {  // Lib.hs:989-1004: foldr over the six rects => last first; strict `<` replaces
       const Q4<T> mn = ldq(sc.cuboids + 2 * (size_t)idx), mx = ldq(sc.cuboids + 2 * (size_t)idx + 1);
-      bool acc = false; T tNew = 0; uint32_t aux = 0;
-#pragma unroll
-      for (int f = 5; f >= 0; --f) {
-        uint32_t plane; T i0, i1, j0, j1, k, t1;
-        cuboidFace<T>(f, mn, mx, plane, i0, i1, j0, j1, k);
-        if (rectT<T>(plane, i0, i1, j0, j1, k, tr.o, tr.d, tr.tmin, tr.tbest, t1)) {
-          if (!acc) { acc = true; tNew = t1; aux = (uint32_t)f; }
-          else if (t1 < tNew) { tNew = t1; aux = (uint32_t)f; }
-        }
+      bool acc; T tNew; uint32_t aux;
+      if constexpr (MODE != MATH_FAST && sizeof(T) == 4 && kPlaneHoist) {
+        const int h = cuboidFacesHoisted(mn, mx, tr.o, tr.d, tr.inv, tr.flags >> F_MODE_SHIFT, tr.tmin, tr.tbest, tNew, aux);
+        acc = h < 0 ? cuboidFacesRolled(mn, mx, tr.o, tr.d, tr.tmin, tr.tbest, tNew, aux) : h > 0;
+      } else {
+        acc = cuboidFaces<T>(mn, mx, tr.o, tr.d, tr.tmin, tr.tbest, tNew, aux);
       }
       if (acc) travAccept<T>(tr, tNew, ref, aux);
     }
@@ -311,7 +335,7 @@ RTB_D void travRun(const DScene<T>& sc, Trav<T>& tr, T time, Rng& rng, Instr<INS
     const int c = stepClass(tr.cur);
     if (c == 0) stepNode<T, INSTR, MODE>(sc, tr, ins);
     else if (c == 1) stepSphere<T, S, INSTR>(sc, tr, time, ins);
-    else if (c == 2) stepRect<T, INSTR>(sc, tr, ins);
+    else if (c == 2) stepRect<T, INSTR, MODE>(sc, tr, ins);
     else stepRare<T, INSTR, MODE>(sc, tr, rng, ins);
   }
 }

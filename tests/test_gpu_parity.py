@@ -314,6 +314,18 @@ def test_hoisted_reciprocal_division_is_ieee(gpu):
     assert checked.value > 200_000_000 and bad.value == 0, (checked.value, bad.value)
 
 
+def test_interval_filtered_slab_test_decides_like_ieee_division(gpu):
+    """The node step decides boxRayIntersect (Lib.hs:798-814) from one-instruction approximate quotients whenever the comparison margin
+    exceeds their proven error bound (rt_device.cuh slabFiltered) and refines only inside the margin: on 2e9 random and adversarial
+    (box, ray, interval) triples every decision the filter takes alone must equal the decision of the three IEEE divisions."""
+    import ctypes as C
+    out = (C.c_uint64 * 3)()
+    assert gpu.core().rt_selftest_box_filter(2_000_000_000, 987654321, out) == 0
+    checked, decided, bad = int(out[0]), int(out[1]), int(out[2])
+    assert checked > 1_900_000_000 and bad == 0, (checked, decided, bad)
+    assert 0.5 < decided / checked < 0.999, (checked, decided)  # the adversarial cases do reach the refined test
+
+
 @pytest.mark.parametrize("name,w,h", [("random", 600, 400), ("cornell", 500, 500), ("next_week_final", 400, 400)])
 def test_full_size_properties(gpu, O, earth, name, w, h):
     """BASELINE.json's full image sizes: (i) the frame is the sum of its sample slices and of its row bands (what spp / tile

@@ -156,13 +156,13 @@ def run_reference(args, W, H, rank):
     tot = sum(times)
     v = args.steps * w * h * spp / tot
     sample = "%dx%d, %d spp per step (full frame, reduced spp), depth 50" % (w, h, spp)
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": "samples/sec", "value": v, "unit": "samples/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * tot / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": SCENE_DOC[args.scene], "scene": args.scene, "width": w, "height": h, "spp_per_step": spp, "max_depth": 50},
         "cpu_baseline": {"value": v, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0}))
+        "gpu_launches": 0})
 
 
 class Ctx:
@@ -364,7 +364,21 @@ def measure(cx, scene, spp, steps, warmup, synth_n=1000, size=None, cpu=True, e2
     return out
 
 
+_OUT = None
+
+
+def emit(obj):
+    """the ONE JSON line, on the process's original stdout"""
+    (_OUT or sys.stdout).write(json.dumps(obj) + "\n")
+    (_OUT or sys.stdout).flush()
+
+
 def main():
+    # stdout carries ONE JSON line: libraries that write to fd 1 (NCCL prints its version banner there) are pointed at stderr
+    global _OUT
+    sys.stdout.flush()
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -398,7 +412,6 @@ def main():
     cx.dev = torch.device("cuda", local)
     gloo = None
     if world > 1:
-        os.environ["NCCL_DEBUG"] = os.environ.get("RTB_NCCL_DEBUG", "WARN")  # keep NCCL's version banner off stdout: ONE JSON line
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=cx.dev)
         gloo = dist.new_group(backend="gloo")  # host-side barrier for the rank-0-only sections (an NCCL barrier would spin on the other GPUs)
@@ -455,7 +468,7 @@ def main():
                 line[k] = head[k]
         if per_scene:
             line["per_scene"] = per_scene
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 

@@ -22,9 +22,10 @@ module LibB200
 #include "rt_abi.h"
 
 import qualified Codec.Picture        as JP (Image (..))
-import           Control.Exception    (bracket, finally)
+import           Control.Exception    (bracket, evaluate, finally)
 import           Control.Monad        (forM, forM_, when)
 import           Data.IORef
+import qualified Data.IntMap.Strict   as IM
 import           Data.Int             (Int32)
 import qualified Data.Vector          as VV
 import qualified Data.Vector.Storable as SV
@@ -36,6 +37,7 @@ import           Foreign.C.Types
 import           Lib                  hiding (length) -- Lib exports its own Vec3 `length` (Lib.hs:13)
 import           Random               (RandGen, randomWord64)
 import           System.IO.Unsafe     (unsafePerformIO)
+import           System.Mem.StableName (StableName, eqStableName, hashStableName, makeStableName)
 
 -- ---------------------------------------------------------------------------------------------------------------------------
 -- foreign imports: one per entry point of include/rt_abi.h that a renderer needs
@@ -92,11 +94,30 @@ data Flat = Flat
   , fTexs       :: Tbl (Word32, Vec3, Word32, Word32, Double)    -- kind, rgb, a, b, scale
   , fPerlin     :: Tbl (VV.Vector Vec3, V.Vector Int, V.Vector Int, V.Vector Int)
   , fImages     :: Tbl (SV.Vector Word8, Int, Int)
+  , fMemoT      :: Memo Texture   -- a Texture / Material / image shared by many objects (one earth map, one glass) is pushed ONCE
+  , fMemoM      :: Memo Material
+  , fMemoI      :: Memo Image
   }
+
+-- Sharing by heap identity: StableName of the evaluated constructor, bucketed by its hash.  Two structurally equal but separately built
+-- values are simply pushed twice (same semantics, a few more rows).
+type Memo a = IORef (IM.IntMap [(StableName a, Word32)])
+
+memoised :: Memo a -> a -> IO Word32 -> IO Word32
+memoised memo x build = do
+  x' <- evaluate x
+  sn <- makeStableName x'
+  seen <- readIORef memo
+  case [i | (s, i) <- IM.findWithDefault [] (hashStableName sn) seen, eqStableName s sn] of
+    (i : _) -> return i
+    []      -> do
+      i <- build
+      modifyIORef' memo (IM.insertWith (++) (hashStableName sn) [(sn, i)])
+      return i
 
 newFlat :: IO Flat
 newFlat = Flat <$> newTbl <*> newTbl <*> newTbl <*> newTbl <*> newTbl <*> newTbl <*> newTbl <*> newTbl <*> newTbl <*> newTbl
-               <*> newTbl <*> newTbl
+               <*> newTbl <*> newTbl <*> newIORef IM.empty <*> newIORef IM.empty <*> newIORef IM.empty
 
 -- ref = kind << 28 | index (include/rt_abi.h RT_REF); the kinds are enum RtHittableKind
 ref :: Word32 -> Word32 -> Word32
@@ -109,25 +130,31 @@ rtNone = #{const RT_NONE}
 -- the flattener: a depth-first walk of Hittable (Lib.hs:521-585), Material (339-345) and Texture (394-419)
 -- ---------------------------------------------------------------------------------------------------------------------------
 flattenT :: Flat -> Texture -> IO Word32
-flattenT f (ConstantColor (Albedo rgb)) = push (fTexs f) (#{const RT_TEX_CONSTANT}, rgb, 0, 0, 0)
-flattenT f (CheckerTexture odd' even') = do
+flattenT f t = memoised (fMemoT f) t (flattenT' f t)
+
+flattenT' :: Flat -> Texture -> IO Word32
+flattenT' f (ConstantColor (Albedo rgb)) = push (fTexs f) (#{const RT_TEX_CONSTANT}, rgb, 0, 0, 0)
+flattenT' f (CheckerTexture odd' even') = do
   o <- flattenT f odd'
   e <- flattenT f even'
   push (fTexs f) (#{const RT_TEX_CHECKER}, Vec3 0 0 0, o, e, 0)
-flattenT f (Perlin ranvec px py pz sc) = do
+flattenT' f (Perlin ranvec px py pz sc) = do
   t <- push (fPerlin f) (ranvec, px, py, pz)
   push (fTexs f) (#{const RT_TEX_PERLIN}, Vec3 0 0 0, t, 0, sc)
-flattenT f (ImageTexture Nothing _ _) = push (fTexs f) (#{const RT_TEX_IMAGE}, Vec3 0 0 0, rtNone, 0, 0) -- renders (0,1,1), Lib.hs:504-505
-flattenT f (ImageTexture (Just (Image im)) w h) = do
-  i <- push (fImages f) (JP.imageData im, w, h) -- tightly packed RGB8, top row first (JuicyPixels)
+flattenT' f (ImageTexture Nothing _ _) = push (fTexs f) (#{const RT_TEX_IMAGE}, Vec3 0 0 0, rtNone, 0, 0) -- renders (0,1,1), Lib.hs:504-505
+flattenT' f (ImageTexture (Just img@(Image im)) w h) = do
+  i <- memoised (fMemoI f) img (push (fImages f) (JP.imageData im, w, h)) -- tightly packed RGB8, top row first (JuicyPixels)
   push (fTexs f) (#{const RT_TEX_IMAGE}, Vec3 0 0 0, i, 0, 0)
 
 flattenM :: Flat -> Material -> IO Word32
-flattenM f (Lambertian t)                   = flattenT f t >>= \ti -> push (fMats f) (#{const RT_LAMBERTIAN}, ti, 0)
-flattenM f (Metal t (Fuzz fz))              = flattenT f t >>= \ti -> push (fMats f) (#{const RT_METAL}, ti, fz)
-flattenM f (Dielectric (RefractiveIdx ior)) = push (fMats f) (#{const RT_DIELECTRIC}, rtNone, ior)
-flattenM f (DiffuseLight t)                 = flattenT f t >>= \ti -> push (fMats f) (#{const RT_DIFFUSE_LIGHT}, ti, 0)
-flattenM f (Isotropic t)                    = flattenT f t >>= \ti -> push (fMats f) (#{const RT_ISOTROPIC}, ti, 0)
+flattenM f m = memoised (fMemoM f) m (flattenM' f m)
+
+flattenM' :: Flat -> Material -> IO Word32
+flattenM' f (Lambertian t)                   = flattenT f t >>= \ti -> push (fMats f) (#{const RT_LAMBERTIAN}, ti, 0)
+flattenM' f (Metal t (Fuzz fz))              = flattenT f t >>= \ti -> push (fMats f) (#{const RT_METAL}, ti, fz)
+flattenM' f (Dielectric (RefractiveIdx ior)) = push (fMats f) (#{const RT_DIELECTRIC}, rtNone, ior)
+flattenM' f (DiffuseLight t)                 = flattenT f t >>= \ti -> push (fMats f) (#{const RT_DIFFUSE_LIGHT}, ti, 0)
+flattenM' f (Isotropic t)                    = flattenT f t >>= \ti -> push (fMats f) (#{const RT_ISOTROPIC}, ti, 0)
 
 flattenR :: Flat -> Rectangle -> IO Word32
 flattenR f (XYRect a0 a1 b0 b1 k m) = flattenM f m >>= \mi -> ref #{const RT_RECT_XY} <$> push (fRects f) ((a0, a1, b0, b1, k), mi)

@@ -512,6 +512,7 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
     if (!c->h_wfCtl) CU(cudaHostAlloc(reinterpret_cast<void**>(&c->h_wfCtl), 2 * sizeof(unsigned long long), cudaHostAllocDefault));
     wfLayout((uint32_t)P, static_cast<char*>(c->wfBlob), &c->wf);
     a.wfMedia = hs.n_media > 0 ? 1u : 0u;
+    a.wfGuideInv = 1.0f / ((float)P * (float)std::max(1u, tuneParam("RTB_WF_GUIDE", 4)));  // a slot asks for 1 / (4 P) of what is left (tools/wf_guide_sweep.py)
     a.wfSort = tuneParam("RTB_WF_SORT", 0);  // measured: the block-level material sort costs what it saves (tools/wf_sweep.py), off by default
     a.shadeMin = tuneParam("RTB_WF_ITEM_MIN", 8);
     const unsigned long long lanes = (unsigned long long)c->numSMs * 8ull * kBlock;

@@ -77,6 +77,10 @@ template <int INSTR> RTB_D void coopCommit(Instr<INSTR>& ins, unsigned committed
   }
 }
 
+#ifndef RTB_COOP_PF
+#define RTB_COOP_PF 0  /* measured (profiles/r2_coop_prefetch_ab.log): 1 / 2 / 4 windows ahead lose 5 / 6 / 7 % at 90 k spheres, 2-4 % at 1 M */
+#endif
+constexpr uint32_t kCoopPrefetch = RTB_COOP_PF;  // windows of 32 records
 // `hit world ray t_min t_max` over the scan stream; the whole warp calls it with identical arguments
 template <class T, class S, int INSTR, int MODE>
 RTB_D void coopTraverse(const DScene<T>& sc, CoopQuery<T>& q, Instr<INSTR>& ins) {
@@ -88,6 +92,11 @@ RTB_D void coopTraverse(const DScene<T>& sc, CoopQuery<T>& q, Instr<INSTR>& ins)
     const bool valid = i < n;
     Q4<T> r0{0, 0, 0, 0}, r1{0, 0, 0, 0};
     if (valid) { r0 = ldq(sc.coop + 2 * (size_t)i); r1 = ldq(sc.coop + 2 * (size_t)i + 1); }
+    // the scan is sequential unless a box fails or a leaf is accepted: pull this lane's record of the window kCoopPrefetch ahead into L1
+    // (one 32-byte sector = both loads) while this window is tested -- the kernel is bound by the L2 latency of these loads
+    if constexpr (kCoopPrefetch > 0) {
+      if (i + 32u * kCoopPrefetch < n) asm volatile("prefetch.global.L1 [%0];" ::"l"(sc.coop + 2 * ((size_t)i + 32u * kCoopPrefetch)));
+    }
     const uint32_t ref = valid ? bitsOf(r1.w) : (K_UNHITTABLE << 28);
     const uint32_t kind = ref >> 28;
     bool ev = false; T tHit = 0; uint32_t skip = 0;

@@ -23,6 +23,7 @@ struct RenderArgs {
   double* out;                     // device: double[H*W*3] radiance sums, accumulated with atomicAdd
   uint32_t* plogPrim; double* plogT; uint32_t plogStride;  // INSTR=3: per-path bounce log [total_paths][plogStride]
   uint32_t wfChunk;                // wavefront: consecutive path indices (= consecutive samples of a pixel) a slot takes at a time
+  float wfGuideInv;                // wavefront: a slot asks for (indices left) * wfGuideInv, at least 1 and at most wfChunk (guided: short drain at the end of the frame)
   uint32_t wfSort;                 // wavefront: shade blocks sort their slots by material (RTB_WF_SORT=0 turns it off for A/B runs)
   uint32_t wfMedia;                // wavefront: the scene has ConstantMedium (the traversal draws from the path's stream)
 };

@@ -152,6 +152,8 @@ RTB_D void lpdfAdvance(const DScene<T>& sc, Trav<T>& tr, PathState<T>& ps, Instr
         e[0] = rc; stT(e + tr.stride, tr.stride, curW * ((T)sz.z / (T)sz.x)); ++lsp;
         e = lightEntry<T>(tr, lbase, lsp);
         e[0] = lc; stT(e + tr.stride, tr.stride, curW * ((T)sz.y / (T)sz.x)); ++lsp;
+      } else {
+        __trap();  // cannot happen: rt_scene_create sizes lightCap from the depth of the lights BVH (a dropped child would bias the pdf silently)
       }
     }
   }

@@ -227,9 +227,14 @@ __global__ void __launch_bounds__(kShadeBlock) wfShadeKernel(const __grid_consta
           uint32_t left = w.chunkLeft[s];
           unsigned long long next = w.chunkNext[s];
           if (left == 0) {
-            next = atomicAdd(w.ctl + 3, (unsigned long long)a.wfChunk);
+            // guided: full chunks while the index space is large, shorter ones towards its end, so that the slots run dry together
+            // (a 32-path chunk taken last is ~200 more rounds at falling occupancy; any split of the index space gives the same frame)
+            const unsigned long long seen = *reinterpret_cast<volatile unsigned long long*>(w.ctl + 3);
+            const float rem = seen < a.total_paths ? __ull2float_rn(a.total_paths - seen) : 0.0f;
+            const uint32_t want = (uint32_t)fminf(fmaxf(rem * a.wfGuideInv, 1.0f), (float)a.wfChunk);
+            next = atomicAdd(w.ctl + 3, (unsigned long long)want);
             if (next >= a.total_paths) { ph = WF_DEAD; break; }
-            left = (next + a.wfChunk <= a.total_paths) ? a.wfChunk : (uint32_t)(a.total_paths - next);
+            left = (next + want <= a.total_paths) ? want : (uint32_t)(a.total_paths - next);
           }
           w.chunkNext[s] = next + 1; w.chunkLeft[s] = left - 1;
           const uint32_t regionW = a.col1 - a.col0;

@@ -237,7 +237,11 @@ template <class T> int buildDevice(const HostScene& h, DevBuffers<T>& db) {
     const double* m = &h.moving[i * 9];
     moving[3 * i] = Q{(T)m[0], (T)m[1], (T)m[2], (T)m[8]};
     moving[3 * i + 1] = Q{(T)m[3], (T)m[4], (T)m[5], (T)m[6]};
-    moving[3 * i + 2] = Q{(T)m[7], B(h.moving_mat[i]), (T)0, (T)0};
+    // exact reciprocal of a power-of-two duration (movingFrac, rt_device.cuh): mantissa 0.5 in T's own rounding, and 1 / d representable
+    const T dur = (T)m[7];
+    int e2 = 0;
+    const bool pow2 = std::isfinite((double)dur) && dur != (T)0 && std::fabs(std::frexp((double)dur, &e2)) == 0.5 && e2 > -100 && e2 < 100;
+    moving[3 * i + 2] = Q{dur, B(h.moving_mat[i]), pow2 ? (T)1 / dur : (T)0, (T)0};
   }
   for (size_t i = 0; i < h.n_rects; ++i) {
     const double* r = &h.rect[i * 5];

@@ -201,7 +201,7 @@ RTB_D void stepSphere(const DScene<T>& sc, Trav<T>& tr, T time, Instr<INSTR>& in
     } else {  // MovingSphere (Lib.hs:1106-1108)
       const Q4<T> a = ldq(sc.moving + 3 * (size_t)idx), b = ldq(sc.moving + 3 * (size_t)idx + 1), c = ldq(sc.moving + 3 * (size_t)idx + 2);
       const V3<T> c0 = mk<T>(a.x, a.y, a.z), c1 = mk<T>(b.x, b.y, b.z);
-      ctr = c0 + scale((time - b.w) / c.x, c1 - c0); rad = a.w;
+      ctr = c0 + scale(movingFrac<T>(time, b.w, c.x, c.z), c1 - c0); rad = a.w;
     }
     T t;
     if (sphereT<T, S>(ctr, rad, tr.o, tr.d, tr.tmin, tr.tbest, t)) { ins.sphereHit(); travAccept<T>(tr, t, ref, 0); }

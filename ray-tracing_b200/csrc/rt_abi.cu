@@ -140,40 +140,55 @@ bool refOk(const HostScene& h, uint32_t ref) {
 // Structural analysis of the hittable DAG: traversal stack need (push/pop discipline of rtb::traverse), open
 // frames, medium nesting, htblSize; detects cycles.  Memoised per ref.
 struct Analysis {
+  // per hittable ref, memoised over the DAG: traversal-stack entries needed, open frames, nested media, htblSize.  Flat tables
+  // indexed by a dense id (a 1 M-sphere scene is 3 M refs: std::map tables made rt_scene_create the slowest part of an e2e step)
   const HostScene& h;
-  std::map<uint32_t, int> stackNeed, frames, media, size;
-  std::map<uint32_t, int> state;  // 1 = in progress, 2 = done
+  size_t base[16];
+  std::vector<int> stackNeedV, sizeV;
+  std::vector<uint8_t> framesV, mediaV, state;  // state: 0 new, 1 in progress, 2 done
   bool cycle = false;
-  explicit Analysis(const HostScene& hs) : h(hs) {}
+  int maxStack = 1, maxFrames = 0, maxMedia = 0;
+  explicit Analysis(const HostScene& hs) : h(hs) {
+    const size_t cnt[16] = {1, hs.n_spheres, hs.n_moving, hs.n_rects, hs.n_rects, hs.n_rects, hs.n_cuboids, hs.n_nodes, hs.n_translates, hs.n_rotates, hs.n_media, 0, 0, 0, 0, 0};
+    size_t tot = 0;
+    for (int k = 0; k < 16; ++k) { base[k] = tot; tot += cnt[k]; }
+    stackNeedV.assign(tot, 0); sizeV.assign(tot, 0); framesV.assign(tot, 0); mediaV.assign(tot, 0); state.assign(tot, 0);
+  }
+  size_t id(uint32_t ref) const { return base[ref >> 28] + ((ref >> 28) == K_UNHITTABLE ? 0 : (ref & kIdxMask)); }  // refs were range-checked (refOk)
+  int size(uint32_t ref) const { return sizeV[id(ref)]; }
   void go(uint32_t ref) {
     if (cycle) return;
-    int& st = state[ref];
-    if (st == 2) return;
-    if (st == 1) { cycle = true; return; }
-    st = 1;
+    const size_t me = id(ref);
+    if (state[me] == 2) return;
+    if (state[me] == 1) { cycle = true; return; }
+    state[me] = 1;
     uint32_t k = ref >> 28, i = ref & kIdxMask;
     int sn = 0, fr = 0, md = 0, sz = 1;
     if (k == K_BVH) {
       uint32_t l = h.node_left[i], r = h.node_right[i];
       go(l); go(r);
       if (cycle) return;
-      sn = std::max(2, std::max(1 + stackNeed[l], stackNeed[r]));
-      fr = std::max(frames[l], frames[r]); md = std::max(media[l], media[r]); sz = (int)h.node_size[i];
+      const size_t il = id(l), ir = id(r);
+      sn = std::max(2, std::max(1 + stackNeedV[il], stackNeedV[ir]));
+      fr = std::max(framesV[il], framesV[ir]); md = std::max(mediaV[il], mediaV[ir]); sz = (int)h.node_size[i];
     } else if (k == K_TRANSLATE || k == K_ROTATE) {
       uint32_t c = k == K_TRANSLATE ? h.translate_child[i] : h.rotate_child[i];
       go(c);
       if (cycle) return;
-      sn = std::max(2, 1 + stackNeed[c]); fr = 1 + frames[c]; md = media[c]; sz = size[c];
+      const size_t ic = id(c);
+      sn = std::max(2, 1 + stackNeedV[ic]); fr = 1 + framesV[ic]; md = mediaV[ic]; sz = sizeV[ic];
     } else if (k == K_MEDIUM) {
       uint32_t c = h.medium_boundary[i];
       go(c);
       if (cycle) return;
-      sn = std::max(2, 1 + stackNeed[c]); fr = frames[c]; md = 1 + media[c]; sz = 1;
+      const size_t ic = id(c);
+      sn = std::max(2, 1 + stackNeedV[ic]); fr = framesV[ic]; md = 1 + mediaV[ic]; sz = 1;
     } else if (k == K_UNHITTABLE) {
       sz = 0;
     }
-    stackNeed[ref] = sn; frames[ref] = fr; media[ref] = md; size[ref] = sz;
-    state[ref] = 2;
+    stackNeedV[me] = sn; framesV[me] = (uint8_t)std::min(fr, 255); mediaV[me] = (uint8_t)std::min(md, 255); sizeV[me] = sz;
+    maxStack = std::max(maxStack, sn); maxFrames = std::max(maxFrames, fr); maxMedia = std::max(maxMedia, md);
+    state[me] = 2;
   }
 };
 int lightDepth(const HostScene& h, uint32_t ref, int d = 0) {
@@ -974,26 +989,22 @@ int rt_scene_create(const RtSceneDesc* d, int device, rt_scene_t* out) {
   an.go(h.world_root); an.go(h.lights_root);
   if (!an.cycle) for (uint32_t i = 0; i < h.n_nodes; ++i) { an.go(h.node_left[i]); an.go(h.node_right[i]); }
   if (an.cycle) return fail(RT_ERR_ARG, "hittable graph has a cycle");
-  int stackNeed = 1, frames = 0, media = 0;
-  for (auto& kv : an.stackNeed) stackNeed = std::max(stackNeed, kv.second);
-  for (auto& kv : an.frames) frames = std::max(frames, kv.second);
-  for (auto& kv : an.media) media = std::max(media, kv.second);
+  const int stackNeed = an.maxStack, frames = an.maxFrames, media = an.maxMedia;
   if (stackNeed > kMaxStack) return fail(RT_ERR_UNSUPPORTED, "scene needs a traversal stack of " + std::to_string(stackNeed) + " entries (limit " + std::to_string(kMaxStack) + ")");
   if (frames > kMaxFrames) return fail(RT_ERR_UNSUPPORTED, "more than " + std::to_string(kMaxFrames) + " nested Translate/Rotate frames");
   if (media > 1) return fail(RT_ERR_UNSUPPORTED, "ConstantMedium nested inside a ConstantMedium boundary");
   if (lightDepth(h, h.lights_root) + 1 > kMaxLightDepth) return fail(RT_ERR_UNSUPPORTED, "lights BVH too deep");
   {  // scan-stream eligibility and size (memoised expansion count; shared subtrees are expanded once per reference)
-    std::map<uint32_t, uint64_t> count;
+    std::vector<uint64_t> count(h.n_nodes, 0);  // per node, 0 = not yet counted
     bool ok = (h.world_root >> 28) == K_BVH;
     std::function<uint64_t(uint32_t)> expand = [&](uint32_t ref) -> uint64_t {
       const uint32_t k = ref >> 28;
       if (k == K_SPHERE || (k >= K_RECT_XY && k <= K_RECT_YZ) || k == K_UNHITTABLE) return 1;
       if (k != K_BVH) { ok = false; return 1; }
-      auto it = count.find(ref);
-      if (it != count.end()) return it->second;
       const uint32_t i = ref & kIdxMask;
+      if (count[i]) return count[i];
       const uint64_t c = 1 + expand(h.node_left[i]) + expand(h.node_right[i]);
-      count[ref] = c;
+      count[i] = c;
       return c;
     };
     const uint64_t total = ok ? expand(h.world_root) : 0;
@@ -1005,7 +1016,7 @@ int rt_scene_create(const RtSceneDesc* d, int device, rt_scene_t* out) {
   h.stackDepth = stackNeed;
   h.lightCap = (h.lights_root >> 28) == K_BVH ? (uint32_t)lightDepth(h, h.lights_root) : 0u;  // DFS over L levels holds at most L entries
   h.node_lsize.resize(h.n_nodes); h.node_rsize.resize(h.n_nodes);
-  for (uint32_t i = 0; i < h.n_nodes; ++i) { h.node_lsize[i] = (uint32_t)an.size[h.node_left[i]]; h.node_rsize[i] = (uint32_t)an.size[h.node_right[i]]; }
+  for (uint32_t i = 0; i < h.n_nodes; ++i) { h.node_lsize[i] = (uint32_t)an.size(h.node_left[i]); h.node_rsize[i] = (uint32_t)an.size(h.node_right[i]); }
 
   // ---- device
   int ndev = 0;

@@ -189,6 +189,18 @@ def roofline_block(scene, W, H, spp, synth_n, work, kernel_ms, peaks, fp32, fast
         if tr.get("lts_bytes") and mem["l2_peak_gbs"]:
             mem["l2_gbs"] = tr["lts_bytes"] / (tr.get("kernel_ms", kernel_ms) / 1e3) / 1e9
             mem["l2_frac_of_l2_peak"] = mem["l2_gbs"] / mem["l2_peak_gbs"]
+    if work.get("kernel") == "wavefront" and work.get("rounds"):
+        # the wavefront frame is ~2 launches per round: DRAM traffic per frame ~ rounds x (one captured full-occupancy round of each kernel);
+        # an upper estimate (the drain rounds move less), reported beside the null per-launch `traffic`
+        tt = _json("profiles/r2_traffic.json") or {}
+        ra, rb = tt.get(scene + "_wfTraverse_round"), tt.get(scene + "_wfShade_round")
+        if ra and rb and all((r["width"], r["height"], r["spp"]) == (W, H, spp) for r in (ra, rb)):
+            per_round = sum(r["dram_bytes_read"] + r["dram_bytes_write"] for r in (ra, rb))
+            mem.update({"wavefront_rounds": work["rounds"], "dram_bytes_per_round_captured": per_round,
+                        "round_ms_captured": ra["kernel_ms"] + rb["kernel_ms"], "dram_bytes_per_frame_estimate": per_round * work["rounds"],
+                        "dram_gbs_estimate": per_round * work["rounds"] / secs / 1e9,
+                        "dram_frac_of_hbm_peak_estimate": per_round * work["rounds"] / secs / 1e9 / hbm_peak,
+                        "source": "profiles/r2_ncu_%s_wfTraverseKernel.txt + _wfShadeKernel.txt (one mid-frame round each, --set full)" % scene})
     if scene == "synthetic":
         # the one memory-side config: 1 M spheres = 33.5 MB of nodes + 16 MB of spheres, L2-resident on B200 (126 MB): node / leaf
         # fetch bandwidth against the measured L2 and HBM peaks
@@ -282,7 +294,8 @@ def measure(cx, scene, spp, steps, warmup, synth_n=1000, size=None, cpu=True, e2
         out = {"scene": scene, "workload": SCENE_DOC[scene] if scene != "synthetic" else SCENE_DOC[scene] + "; %d spheres, %dx%d x %d spp" % (synth_n * synth_n, W, H, spp),
                "width": W, "height": H, "spp_per_gpu_per_step": spp, "steps": steps, "warmup": warmup,
                "value": value, "unit": "samples/s", "ms_per_step": ms / steps, "kernel_ms": kernel_ms, "finite_pixel_fraction": finite_frac,
-               "roofline": roofline_block(scene, W, H, spp, synth_n, work, kernel_ms, cx.peaks, cx.fp32, args.fast), "gpu_launches": int(sum(launches))}
+               "roofline": roofline_block(scene, W, H, spp, synth_n, dict(work, rounds=(float(np.mean(launches)) - 1.0) / 2.0 if work.get("kernel") == "wavefront" else None),
+                                          kernel_ms, cx.peaks, cx.fp32, args.fast), "gpu_launches": int(sum(launches))}
         if scene == "synthetic":
             out["host_scene_build_s"] = host_build_s
 

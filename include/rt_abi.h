@@ -177,7 +177,7 @@ typedef struct RtRenderParams {
   int32_t device;             /* CUDA device ordinal, -1 = current */
   uint32_t n_gpus;            /* rt_render only: devices the call shards the frame over.  0 = the library default (1 until rt_init
                                  changes it), k = devices 0..k-1 plus the scene's own.  The scene is replicated onto them on first use,
-                                 samples are split into contiguous slices (row bands when sample_count < devices), the partial
+                                 samples are split into contiguous slices (interleaved rows when sample_count < devices), the partial
                                  framebuffers are summed onto the scene's device over NVLink and copied to the host once. */
 } RtRenderParams;
 

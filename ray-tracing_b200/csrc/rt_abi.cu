@@ -476,7 +476,7 @@ int wavefrontFinishAll(const HostScene& hs, DeviceCtx* const* ctx, int n) {
 }
 
 int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, double* d_out, cudaStream_t st, int instr, int* gridOut, const PathLog* plog = nullptr,
-                 uint32_t* kindOut = nullptr, bool wfDefer = false) {
+                 uint32_t* kindOut = nullptr, bool wfDefer = false, uint32_t rowStep = 1) {
   if ((q.flags & RT_FLAG_WAVEFRONT) && !wavefrontCapable(q, instr))
     return fail(RT_ERR_UNSUPPORTED, "RT_FLAG_WAVEFRONT: fp32 / mixed arithmetic with literal math and no instrumentation only");
   if ((q.flags & RT_FLAG_COOP) && !hs.coopEligible)
@@ -489,9 +489,9 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
   if (q.sample_count == 0) return RT_OK;
   RenderArgs a{};
   a.W = q.width; a.H = q.height; a.s0 = q.sample_offset; a.ns = q.sample_count; a.maxDepth = q.max_depth;
-  a.row0 = q.row0; a.row1 = q.row1; a.col0 = q.col0; a.col1 = q.col1;
+  a.row0 = q.row0; a.row1 = q.row1; a.col0 = q.col0; a.col1 = q.col1; a.rowStep = std::max(1u, rowStep);
   a.seed = q.seed;
-  a.total_paths = (unsigned long long)(q.row1 - q.row0) * (q.col1 - q.col0) * q.sample_count;
+  a.total_paths = (unsigned long long)((q.row1 - q.row0 + a.rowStep - 1) / a.rowStep) * (q.col1 - q.col0) * q.sample_count;
   // chunk: ~1024 paths, halved until there are at least 8 chunks per warp slot for balance, down to 4 paths: launches with few, very
   // long paths (the cfg5 sample: seconds per path) are tail-bound, and a warp that refills 4 lanes at a time keeps its lanes busier than
   // one that waits for a 32-path chunk to drain (tools/chunk_probe.py: 90 k spheres, 480x270x1: 1424 -> 1242 ms; results are identical)
@@ -532,7 +532,7 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
     wfLayout((uint32_t)P, static_cast<char*>(c->wfBlob), &c->wf);
     a.wfMedia = hs.n_media > 0 ? 1u : 0u;
     a.wfGuideInv = 1.0f / ((float)P * (float)std::max(1u, tuneParam("RTB_WF_GUIDE", 4)));  // a slot asks for 1 / (4 P) of what is left (tools/wf_guide_sweep.py)
-    a.wfSort = tuneParam("RTB_WF_SORT", 0);  // measured: the block-level material sort costs what it saves (tools/wf_sweep.py), off by default
+    a.wfSort = tuneParam("RTB_WF_SORT", 1);  // block-level material sort of the shade kernel: +4 % once the drain is short (profiles/r2_wf_sort_probe.log; it measured neutral while the drain dominated)
     a.shadeMin = tuneParam("RTB_WF_ITEM_MIN", 8);
     const unsigned long long lanes = (unsigned long long)c->numSMs * 8ull * kBlock;
     a.chunk = (uint32_t)std::max<unsigned long long>(32, std::min<unsigned long long>(256, P / std::max<unsigned long long>(1, lanes / 32 * 4)));
@@ -574,7 +574,7 @@ int ensureHostStaging(SceneEntry* e, size_t elems) {
   return RT_OK;
 }
 
-// ---- multi-GPU inside rt_render: the frame's samples are split into contiguous slices over the devices (row bands
+// ---- multi-GPU inside rt_render: the frame's samples are split into contiguous slices over the devices (interleaved rows
 // when there are fewer samples than devices), every device renders its share into its own double framebuffer on its own stream, and
 // the partial sums are added onto the scene's device: by ONE kernel there that reads the peers' buffers over NVLink (peer access),
 // or by ncclReduce when rt_init asked for NCCL, or through staged peer copies when the devices cannot address each other.
@@ -640,21 +640,23 @@ int renderMulti(SceneEntry* e, const RtRenderParams& q, int nGpus, double* out, 
   const uint32_t rows = q.row1 - q.row0;
   for (int k = 0; k < n; ++k) {
     RtRenderParams qk = q;
+    uint32_t rowStep = 1;
     if (bySamples) {
       const uint32_t base = q.sample_count / n, rem = q.sample_count % n;
       qk.sample_offset = q.sample_offset + k * base + std::min<uint32_t>(k, rem);
       qk.sample_count = base + ((uint32_t)k < rem ? 1u : 0u);
     } else {
-      const uint32_t base = rows / n, rem = rows % n;
-      qk.row0 = q.row0 + k * base + std::min<uint32_t>(k, rem);
-      qk.row1 = qk.row0 + base + ((uint32_t)k < rem ? 1u : 0u);
-      if (qk.row1 <= qk.row0) qk.sample_count = 0;
+      // fewer samples than devices: device k takes rows row0 + k, row0 + k + n, ... (interleaved: neighbouring rows cost alike, bands do not --
+      // the cfg5 sample's upper band was 30 % cheaper than its lower one)
+      qk.row0 = q.row0 + (uint32_t)k;
+      rowStep = (uint32_t)n;
+      if ((uint32_t)k >= rows) qk.sample_count = 0;
     }
     CU(cudaSetDevice(devs[k]));
     CU(cudaMemsetAsync(ctx[k]->d_fb, 0, elems * sizeof(double), ctx[k]->stream));
     CU(cudaEventRecord(ctx[k]->evStart, ctx[k]->stream));
     ctx[k]->wfPending = false;
-    if ((rc = renderLaunch(e->hs, ctx[k], qk, ctx[k]->d_fb, ctx[k]->stream, 0, nullptr, nullptr, &kernelKind, /*wfDefer=*/true))) return rc;
+    if ((rc = renderLaunch(e->hs, ctx[k], qk, ctx[k]->d_fb, ctx[k]->stream, 0, nullptr, nullptr, &kernelKind, /*wfDefer=*/true, rowStep))) return rc;
     if (!ctx[k]->wfPending) CU(cudaEventRecord(ctx[k]->evDone, ctx[k]->stream));
   }
   {  // wavefront shares: every device has its first batch of rounds queued; top them up round-robin until each frame is finished
@@ -1129,7 +1131,7 @@ int rt_render_device_static(rt_scene_t scene, const RtRenderParams* params, doub
     const HostScene& hs = e->hs;
     RenderArgs a{};  // the same launch parameters as renderLaunch's renderKernel branch (results never depend on the scheduler knobs)
     a.W = q.width; a.H = q.height; a.s0 = q.sample_offset; a.ns = q.sample_count; a.maxDepth = q.max_depth;
-    a.row0 = q.row0; a.row1 = q.row1; a.col0 = q.col0; a.col1 = q.col1;
+    a.row0 = q.row0; a.row1 = q.row1; a.col0 = q.col0; a.col1 = q.col1; a.rowStep = 1;
     a.seed = q.seed;
     a.total_paths = (unsigned long long)(q.row1 - q.row0) * (q.col1 - q.col0) * q.sample_count;
     const unsigned long long warps = (unsigned long long)c->numSMs * 16ull;

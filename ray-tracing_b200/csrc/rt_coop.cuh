@@ -245,7 +245,7 @@ __global__ void __launch_bounds__(kBlock) renderKernelCoop(const __grid_constant
       break;
     }
     const uint32_t pl = (uint32_t)(idx / a.ns), s = a.s0 + (uint32_t)(idx % a.ns);
-    const uint32_t row = a.row0 + pl / regionW, col = a.col0 + pl % regionW;
+    const uint32_t row = a.row0 + (pl / regionW) * a.rowStep, col = a.col0 + pl % regionW;
     const uint32_t pixel = row * a.W + col;
     if (pixel != accPix) {
       if (lane == 0 && accPix != kNone) { atomicAdd(a.out + (size_t)accPix * 3, acc0); atomicAdd(a.out + (size_t)accPix * 3 + 1, acc1); atomicAdd(a.out + (size_t)accPix * 3 + 2, acc2); }

@@ -10,6 +10,7 @@ struct RenderArgs {
   uint32_t s0, ns;                 // sample range [s0, s0+ns)
   uint32_t maxDepth;
   uint32_t row0, row1, col0, col1; // region (rows counted from the top)
+  uint32_t rowStep;                // rows row0, row0 + rowStep, ... < row1 (1 = every row; n = the interleaved row share of one of n devices)
   uint32_t chunk;                  // path indices a warp takes per atomic (at most; guided: fewer towards the end of the index space)
   uint32_t chunkMin, chunkDiv;     // smallest chunk; a warp asks for (indices left) / chunkDiv
   uint32_t stackCap;               // traversal stack entries per thread (set by the launcher)

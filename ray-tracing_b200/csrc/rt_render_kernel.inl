@@ -283,7 +283,7 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::v) renderKernel(const __
           // path index -> (pixel of the region, sample); consecutive indices = consecutive samples of one pixel
           const uint32_t off = ws[1] + cNext + rank;
           const uint32_t pl = ws[0] + off / a.ns, s = a.s0 + off % a.ns;
-          const uint32_t row = a.row0 + pl / regionW, col = a.col0 + pl % regionW;
+          const uint32_t row = a.row0 + (pl / regionW) * a.rowStep, col = a.col0 + pl % regionW;
           const uint32_t pixel = row * a.W + col;
           if (pixel != tr.xw(XW_ACCPIX)) {
             accFlush<T>(tr, a.out);

@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(kShadeBlock) wfShadeKernel(const __grid_consta
           w.chunkNext[s] = next + 1; w.chunkLeft[s] = left - 1;
           const uint32_t regionW = a.col1 - a.col0;
           const uint32_t pl = (uint32_t)(next / a.ns), smp = a.s0 + (uint32_t)(next % a.ns);
-          const uint32_t row = a.row0 + pl / regionW, col = a.col0 + pl % regionW;
+          const uint32_t row = a.row0 + (pl / regionW) * a.rowStep, col = a.col0 + pl % regionW;
           const uint32_t pixel = row * a.W + col;
           const uint32_t apx = w.accPix[s];
           if (pixel != apx) {

@@ -1,6 +1,6 @@
 """Multi-GPU INSIDE the C ABI: one process, one rt_render call, n devices.  The reference parallelises inside
 its one pure entry point (runRender sparks, Lib.hs:1519-1520; called once from app/Main.hs:58), so the drop-in shards inside the
-call: the scene is replicated, samples are split into contiguous slices (row bands when there are fewer samples than devices) and
+call: the scene is replicated, samples are split into contiguous slices (interleaved rows when there are fewer samples than devices) and
 the partial double framebuffers are summed onto the scene's device by the library's peer-memory kernel over NVLink, or by
 ncclReduce after rt_init(.., RT_INIT_NCCL).  Because sample s of pixel p owns its stream, the n-device frame equals the 1-device
 frame up to the order of the double additions (1e-12).  Needs >= 2 visible devices: the tests skip on a single-GPU box (the

@@ -15,6 +15,9 @@ for spec in sys.argv[2:]:
     total = len(parts) > 5 and parts[5] == "sum"
     raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
+    if not rows or "Kernel Name" not in rows[0]:
+        print("skipping %s: no report at %s" % (key, rep), file=sys.stderr)  # a capture that timed out must not cost the others
+        continue
     hdr = rows[0]
     iK = hdr.index("Kernel Name")
     ent = {"width": W, "height": H, "spp": spp, "report": rep.split("/")[-1], "kernels": []}

@@ -457,8 +457,11 @@ def main():
                     ("cfg4", "cornell", 1000, small, 2, 1000, None), ("cfg5_90k", "synthetic", 1, 2, 1, 300, (480, 270)),
                     ("cfg5_1m", "synthetic", 1, 1, 1, 1000, (240, 135))]
         else:
+            # cfg5 at N > 1: 8 spp of the bounded 240x135 sample.  One path of this scene is ~0.3 s of one warp, so a 1-spp frame (32 400 paths)
+            # cannot be split 8 ways (profiles/r2_bench_default_n8_1spp.json: efficiency 0.21, every GPU waits for its slowest path); 8 spp is
+            # the smallest frame whose split leaves every device the single-GPU sample's number of paths
             plan = [("cfg3", "next_week_final", 256, 2, 1, 1000, None), ("cfg4", "cornell", 1000, 2, 1, 1000, None),
-                    ("cfg5_1m", "synthetic", 1, 1, 1, 1000, (240, 135))]
+                    ("cfg5_1m", "synthetic", 8, 1, 1, 1000, (240, 135))]
         for key, sc, s, st, wu, sn, size in plan:
             r = measure(cx, sc, s, st, wu, synth_n=sn, size=size)
             if rank == 0:

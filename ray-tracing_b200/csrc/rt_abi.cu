@@ -585,9 +585,7 @@ int ensureReplica(SceneEntry* e, int device, DeviceCtx** out) {
     if (!slot) {
       slot.reset(new DeviceCtx());
       slot->device = device;
-      cudaDeviceProp prop;
-      CU(cudaGetDeviceProperties(&prop, device));
-      slot->numSMs = prop.multiProcessorCount;
+      CU(cudaDeviceGetAttribute(&slot->numSMs, cudaDevAttrMultiProcessorCount, device));  // one attribute: cudaGetDeviceProperties costs milliseconds per call
     }
     *out = slot.get();
   }
@@ -1027,9 +1025,7 @@ int rt_scene_create(const RtSceneDesc* d, int device, rt_scene_t* out) {
   if (device >= ndev) return fail(RT_ERR_ARG, "device ordinal out of range");
   CU(cudaSetDevice(device));
   e->main.device = device;
-  cudaDeviceProp prop;
-  CU(cudaGetDeviceProperties(&prop, device));
-  e->main.numSMs = prop.multiProcessorCount;
+  CU(cudaDeviceGetAttribute(&e->main.numSMs, cudaDevAttrMultiProcessorCount, device));
   int rc = buildDevice<float>(h, e->main.f32);  // the production layout is uploaded eagerly; fp64 on first use
   if (rc) return rc;
   std::lock_guard<std::mutex> lk(g_mu);

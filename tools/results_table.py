@@ -65,8 +65,11 @@ def table():
                 r["achieved"], r["frac"], r["peak"], r["l2"]["frac"], r["l2"]["peak"],
                 ("%.2f GB / launch" % (r["traffic"] / 1e9)) if r.get("traffic") else "n/a")
         else:
+            est = r.get("memory", {}).get("dram_bytes_per_frame_estimate")
+            dram = ("%.1f MB / launch" % (r["traffic"] / 1e6)) if r.get("traffic") else (
+                "≈ %.0f GB / frame (%.0f rounds × one captured round of both kernels) = %.2f of HBM peak" % (est / 1e9, r["memory"]["wavefront_rounds"], r["memory"]["dram_frac_of_hbm_peak_estimate"]) if est else "n/a")
             roof = "%.2f of %.1f TFLOP/s non-FMA issue = **%.3f** (%.3f of FFMA peak); DRAM %s" % (
-                r["achieved"], r["peak"], r["frac"], r.get("frac_of_ffma_peak", 0), ("%.1f MB / launch" % (r["traffic"] / 1e6)) if r.get("traffic") else "n/a")
+                r["achieved"], r["peak"], r["frac"], r.get("frac_of_ffma_peak", 0), dram)
         print("| %s | %s | %s | %.1f | %s | %s (%d threads) | %.0f× | %s |" % (name, r.get("kernel", "?"), fmt(v["value"]), v["ms_per_step"], fmt(e["value"]), fmt(c["value"]), c["cores"],
                                                                   e["value"] / c["value"], roof))
     ck = d.get("clocks", {})

@@ -61,6 +61,39 @@ template <class T> struct DevBuffers {
   ~DevBuffers() { if (blob) cudaFree(blob); }
 };
 
+// The wavefront's path-state slots (~360 MB on a B200) outlive their scene in a small per-device pool: a host that creates a scene per
+// frame (bench.py's e2e loop, a progressive viewer) otherwise pays a cudaMalloc + cudaFree of the blob per frame.  Blobs are handed out
+// whole and exclusively (a DeviceCtx owns what it took until it is destroyed), at most kKeep per device are kept, rt_shutdown frees them.
+struct ScratchPool {
+  struct Item { int device; void* p; size_t bytes; };
+  static constexpr size_t kKeep = 2;
+  std::mutex mu;
+  std::vector<Item> items;
+  void* take(int device, size_t need, size_t* got) {
+    std::lock_guard<std::mutex> lk(mu);
+    int best = -1;
+    for (size_t i = 0; i < items.size(); ++i)
+      if (items[i].device == device && items[i].bytes >= need && (best < 0 || items[i].bytes < items[(size_t)best].bytes)) best = (int)i;
+    if (best < 0) return nullptr;
+    void* p = items[(size_t)best].p; *got = items[(size_t)best].bytes;
+    items.erase(items.begin() + best);
+    return p;
+  }
+  void give(int device, void* p, size_t bytes) {
+    std::lock_guard<std::mutex> lk(mu);
+    size_t have = 0;
+    for (const Item& it : items) have += it.device == device;
+    if (have >= kKeep) { cudaFree(p); return; }
+    items.push_back(Item{device, p, bytes});
+  }
+  void clear() {
+    std::lock_guard<std::mutex> lk(mu);
+    for (const Item& it : items) cudaFree(it.p);
+    items.clear();
+  }
+};
+ScratchPool g_scratch;  // defined before the scene table: destroyed after it at exit (nothing is freed then, the context is going away)
+
 // everything a scene owns on ONE device: the packed scene (fp32 eagerly, fp64 on first use), the work counters, a framebuffer
 struct DeviceCtx {
   int device = 0, numSMs = 148;
@@ -78,7 +111,10 @@ struct DeviceCtx {
   ~DeviceCtx() {
     if (d_counter) cudaFree(d_counter);
     if (d_fb) cudaFree(d_fb);
-    if (wfBlob) cudaFree(wfBlob);
+    if (wfBlob) {  // cudaFree would have waited for the device; a pooled blob may be handed to another scene at once, so wait here
+      int cur = 0; cudaGetDevice(&cur); cudaSetDevice(device); cudaDeviceSynchronize(); cudaSetDevice(cur);
+      g_scratch.give(device, wfBlob, wfBytes);
+    }
     if (h_wfCtl) cudaFreeHost(h_wfCtl);
     if (wfProbe) cudaEventDestroy(wfProbe);
     if (evStart) cudaEventDestroy(evStart);
@@ -525,8 +561,9 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
     if (c->wfBytes < bytes) {
       if (c->wfBlob) cudaFree(c->wfBlob);
       c->wfBlob = nullptr; c->wfBytes = 0;
-      CU(cudaMalloc(&c->wfBlob, bytes));
-      c->wfBytes = bytes;
+      size_t got = 0;
+      if (void* pooled = g_scratch.take(c->device, bytes, &got)) { c->wfBlob = pooled; c->wfBytes = got; }
+      else { CU(cudaMalloc(&c->wfBlob, bytes)); c->wfBytes = bytes; }
     }
     if (!c->h_wfCtl) CU(cudaHostAlloc(reinterpret_cast<void**>(&c->h_wfCtl), 2 * sizeof(unsigned long long), cudaHostAllocDefault));
     wfLayout((uint32_t)P, static_cast<char*>(c->wfBlob), &c->wf);
@@ -1284,6 +1321,7 @@ void rt_shutdown(void) {
     std::lock_guard<std::mutex> lk(g_mu);
     g_scenes.clear();
   }
+  g_scratch.clear();
   std::lock_guard<std::mutex> lk(g_multi.mu);
   for (void* c : g_multi.comms) if (c && g_multi.commDestroy) g_multi.commDestroy(c);
   g_multi.comms.clear(); g_multi.wantNccl = false; g_multi.defaultGpus = 1;

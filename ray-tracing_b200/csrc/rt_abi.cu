@@ -244,6 +244,17 @@ struct PinnedStage {
   std::mutex mu; char* p = nullptr; size_t cap = 0;
   ~PinnedStage() { if (p) cudaFreeHost(p); }
 } g_stage;
+// host-side packing of large scenes (10^6 spheres: ~130 MB of records) over a few threads; small scenes stay on the calling thread
+template <class F> void parallelFor(size_t n, F f, size_t kMin = 1u << 16) {
+  const unsigned hw = std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
+  const size_t parts = std::min<size_t>(hw, n / kMin);
+  if (parts <= 1) { f((size_t)0, n); return; }
+  std::vector<std::thread> th;
+  for (size_t p = 1; p < parts; ++p) th.emplace_back([=] { f(n * p / parts, n * (p + 1) / parts); });
+  f((size_t)0, n / parts);
+  for (auto& t : th) t.join();
+}
+
 struct BlobLayout {
   struct Piece { size_t off; const void* src; size_t bytes; };
   std::vector<Piece> pieces; size_t total = 0;
@@ -273,7 +284,8 @@ template <class T> int buildDevice(const HostScene& h, DevBuffers<T>& db) {
   std::vector<uint4> nsz(h.n_nodes);
   std::vector<uint8_t> pperm(768 * (size_t)h.n_perlin);
   const int pmask = pairMask(h);
-  for (size_t i = 0; i < h.n_nodes; ++i) {
+  parallelFor(h.n_nodes, [&](size_t i0, size_t i1) {
+  for (size_t i = i0; i < i1; ++i) {
     const double* b = &h.node_box[i * 6];
     // both children leaves of one step class (sphere-like, or rect / cuboid): mark the pair (rt_device.cuh kPairBit)
     auto leafClass = [](uint32_t r) { uint32_t k = r >> 28; return (k == K_SPHERE || k == K_MOVING) ? 1 : ((k >= K_RECT_XY && k <= K_CUBOID) ? 2 : 0); };
@@ -283,7 +295,10 @@ template <class T> int buildDevice(const HostScene& h, DevBuffers<T>& db) {
     nodes[2 * i + 1] = Q{(T)b[3], (T)b[4], (T)b[5], B(h.node_right[i])};
     nsz[i] = make_uint4(h.node_size[i], h.node_lsize[i], h.node_rsize[i], 0);
   }
-  for (size_t i = 0; i < h.n_spheres; ++i) { const double* s = &h.sphere_cr[i * 4]; spheres[i] = Q{(T)s[0], (T)s[1], (T)s[2], (T)s[3]}; }
+  });
+  parallelFor(h.n_spheres, [&](size_t i0, size_t i1) {
+    for (size_t i = i0; i < i1; ++i) { const double* sp = &h.sphere_cr[i * 4]; spheres[i] = Q{(T)sp[0], (T)sp[1], (T)sp[2], (T)sp[3]}; }
+  });
   for (size_t i = 0; i < h.n_moving; ++i) {
     const double* m = &h.moving[i * 9];
     moving[3 * i] = Q{(T)m[0], (T)m[1], (T)m[2], (T)m[8]};
@@ -319,30 +334,37 @@ template <class T> int buildDevice(const HostScene& h, DevBuffers<T>& db) {
   // (Lib.hs:971-988) — every node carrying the index of the first record behind its subtree
   std::vector<Q> coop;
   if (h.coopEligible) {
-    coop.reserve(2 * (size_t)h.coopRecords);
-    std::function<void(uint32_t)> emit = [&](uint32_t ref) {
-      const uint32_t k = ref >> 28, i = ref & kIdxMask;
-      const size_t at = coop.size();
+    coop.resize(2 * (size_t)h.coopRecords);
+    size_t at = 0;  // records written
+    // explicit stack instead of recursion: an entry is a ref to emit, or (high bit set) a node record waiting for the end of its subtree
+    std::vector<uint64_t> todo;
+    todo.push_back(h.world_root);
+    const uint64_t kClose = 1ull << 63;
+    while (!todo.empty()) {
+      const uint64_t e = todo.back(); todo.pop_back();
+      if (e & kClose) { coop[2 * (size_t)(e & ~kClose)].w = B((uint32_t)at); continue; }  // first record behind the subtree
+      const uint32_t ref = (uint32_t)e, k = ref >> 28, i = ref & kIdxMask;
+      Q* r = &coop[2 * at];
       if (k == K_BVH) {
         const double* b = &h.node_box[(size_t)i * 6];
-        coop.push_back(Q{(T)b[0], (T)b[1], (T)b[2], B(0u)});
-        coop.push_back(Q{(T)b[3], (T)b[4], (T)b[5], B(ref)});
-        emit(h.node_left[i]); emit(h.node_right[i]);
-        coop[at].w = B((uint32_t)(coop.size() / 2));
+        r[0] = Q{(T)b[0], (T)b[1], (T)b[2], B(0u)};
+        r[1] = Q{(T)b[3], (T)b[4], (T)b[5], B(ref)};
+        todo.push_back(kClose | (uint64_t)at);
+        todo.push_back(h.node_right[i]); todo.push_back(h.node_left[i]);  // left subtree first (Lib.hs:971-988)
       } else if (k == K_SPHERE) {
         const double* sp = &h.sphere_cr[(size_t)i * 4];
-        coop.push_back(Q{(T)sp[0], (T)sp[1], (T)sp[2], (T)sp[3]});
-        coop.push_back(Q{(T)0, (T)0, (T)0, B(ref)});
+        r[0] = Q{(T)sp[0], (T)sp[1], (T)sp[2], (T)sp[3]};
+        r[1] = Q{(T)0, (T)0, (T)0, B(ref)};
       } else if (k >= K_RECT_XY && k <= K_RECT_YZ) {
-        const double* r = &h.rect[(size_t)i * 5];
-        coop.push_back(Q{(T)r[0], (T)r[1], (T)r[2], (T)r[3]});
-        coop.push_back(Q{(T)r[4], (T)0, (T)0, B(ref)});
+        const double* rc = &h.rect[(size_t)i * 5];
+        r[0] = Q{(T)rc[0], (T)rc[1], (T)rc[2], (T)rc[3]};
+        r[1] = Q{(T)rc[4], (T)0, (T)0, B(ref)};
       } else {  // Unhittable
-        coop.push_back(Q{(T)0, (T)0, (T)0, (T)0});
-        coop.push_back(Q{(T)0, (T)0, (T)0, B(ref)});
+        r[0] = Q{(T)0, (T)0, (T)0, (T)0};
+        r[1] = Q{(T)0, (T)0, (T)0, B(ref)};
       }
-    };
-    emit(h.world_root);
+      ++at;
+    }
   }
   DScene<T>& sc = db.sc;
   BlobLayout L;
@@ -365,7 +387,8 @@ template <class T> int buildDevice(const HostScene& h, DevBuffers<T>& db) {
       CU(cudaHostAlloc(reinterpret_cast<void**>(&g_stage.p), total, cudaHostAllocDefault));
       g_stage.cap = total;
     }
-    for (const auto& pc : L.pieces) if (pc.src) std::memcpy(g_stage.p + pc.off, pc.src, pc.bytes);
+    for (const auto& pc : L.pieces) if (pc.src)
+      parallelFor(pc.bytes, [&](size_t b0, size_t b1) { std::memcpy(g_stage.p + pc.off + b0, static_cast<const char*>(pc.src) + b0, b1 - b0); }, (size_t)4 << 20);
     for (size_t i = 0; i < h.n_images; ++i) {  // RGB8 -> uchar4 directly in the staging buffer
       uchar4* px = reinterpret_cast<uchar4*>(g_stage.p + oImg[i]);
       const size_t npx = (size_t)h.image_w[i] * h.image_h[i];
@@ -537,7 +560,7 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
   while (chunk > chunkMin && a.total_paths / chunk < warps * 8ull) chunk /= 2;
   a.chunk = (uint32_t)chunk;
   a.chunkMin = (uint32_t)std::min<unsigned long long>(chunk, std::max(chunkMin, (unsigned long long)tuneParam("RTB_CHUNK_TAIL", 32)));
-  a.chunkDiv = (uint32_t)std::max<unsigned long long>(1, warps * tuneParam("RTB_CHUNK_DIV", 2));
+  a.chunkDiv = (uint32_t)std::max<unsigned long long>(1, warps * tuneParam("RTB_CHUNK_DIV", 8));  // 8: cfg3 +15 % over 2 (its 1024-path chunks are 170 ms of warp time), others -0.2 % (profiles/r2_chunk_div_probe.log)
   // scheduler thresholds (rt_render_kernel.inl): single rects are cheap steps and worth running for 3 lanes, cuboid-heavy scenes batch
   // 6; media make the rare class frequent (3 rare steps per medium visit) and worth running for 4 lanes.  Measured on the
   // reference scenes (tools/knob_sweep.py); results never depend on these.
@@ -1172,7 +1195,7 @@ int rt_render_device_static(rt_scene_t scene, const RtRenderParams* params, doub
     while (chunk > 4 && a.total_paths / chunk < warps * 8ull) chunk /= 2;
     a.chunk = (uint32_t)chunk;
     a.chunkMin = (uint32_t)std::min<unsigned long long>(chunk, 32);
-    a.chunkDiv = (uint32_t)std::max<unsigned long long>(1, warps * 2);
+    a.chunkDiv = (uint32_t)std::max<unsigned long long>(1, warps * 8);
     a.shadeMin = 16; a.rectMin = hs.n_cuboids > hs.n_rects ? 6u : 3u; a.rareMin = hs.n_media > 0 ? 4u : 8u; a.keepNode = 12; a.keepLeaf = 8;
     a.lightCap = hs.lightCap;
     a.counter = scratch; a.ctr = nullptr; a.out = fb;

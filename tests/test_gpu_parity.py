@@ -102,6 +102,25 @@ def test_trace_bit_exact_90k_spheres(gpu, O, prec):
     assert np.array_equal(g["rec"][:, :7], o["rec"][:, :7])
 
 
+def test_trace_bit_exact_160k_spheres_parallel_upload(gpu, O):
+    """synth_n = 400: 160 000 spheres, 262 143 nodes — large enough that rt_scene_create packs the node / sphere records and fills the
+    staging buffer over several host threads (rt_abi.cu parallelFor) and emits a 524 287-record scan stream: the upload must be the
+    same scene (hit, primitive, t / p / normal, visit count and hash bit-exact against the oracle)."""
+    osc = O.OracleScene("synthetic", synth_n=400)
+    rays = _rays(O, osc, n_rand=200)[::6].astype(np.float32).astype(np.float64)
+    hs = gpu.HostScene("synthetic", synth_n=400)
+    ds = hs.upload(W, H)
+    g = ds.trace(rays, precision=gpu.PREC_MIXED, seed=9, log_stride=64)
+    gn = ds.trace(rays, precision=gpu.PREC_MIXED, seed=9, log_stride=64, flags=gpu.FLAG_NO_COOP)  # the per-lane kernel reads nodes / spheres, not the stream
+    ds.destroy()
+    o = osc.trace(rays, prec=O.PREC_MIXED, seed=9, log_stride=64)
+    assert len(rays) >= 300 and o["nvisit"].mean() > 40000
+    for k in ("hit", "prim", "mat", "front", "nvisit", "vhash", "vlog"):
+        assert np.array_equal(g[k], o[k]), k
+        assert np.array_equal(gn[k], o[k]), k
+    assert np.array_equal(g["rec"][:, :7], o["rec"][:, :7]) and np.array_equal(gn["rec"][:, :7], o["rec"][:, :7])
+
+
 @pytest.mark.parametrize("name", NO_MEDIA)
 def test_fp32_traversal_agrees_with_reference_double(gpu, O, oracle_scene, dev_scene, name):
     """fp32 device traversal vs the reference's Double arithmetic: agreement rate of hit id and visit order (grazing rays differ)."""

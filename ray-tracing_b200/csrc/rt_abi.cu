@@ -555,7 +555,7 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
   // long paths (the cfg5 sample: seconds per path) are tail-bound, and a warp that refills 4 lanes at a time keeps its lanes busier than
   // one that waits for a 32-path chunk to drain (tools/chunk_probe.py: 90 k spheres, 480x270x1: 1424 -> 1242 ms; results are identical)
   unsigned long long warps = (unsigned long long)c->numSMs * 16ull;
-  unsigned long long chunk = 1024;
+  unsigned long long chunk = std::max(1u, tuneParam("RTB_CHUNK_MAX", 1024));
   const unsigned long long chunkMin = std::max(1u, tuneParam("RTB_CHUNK_MIN", 4));
   while (chunk > chunkMin && a.total_paths / chunk < warps * 8ull) chunk /= 2;
   a.chunk = (uint32_t)chunk;

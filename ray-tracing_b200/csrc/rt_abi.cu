@@ -567,7 +567,10 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
   a.shadeMin = tuneParam("RTB_SHADE_MIN", 16);
   a.rectMin = std::max(1u, tuneParam("RTB_RECT_MIN", hs.n_cuboids > hs.n_rects ? 6u : 3u));
   a.rareMin = std::max(1u, tuneParam("RTB_RARE_MIN", hs.n_media > 0 ? 4u : 8u));
-  a.keepNode = std::max(1u, tuneParam("RTB_KEEP_NODE", 12)); a.keepLeaf = std::max(1u, tuneParam("RTB_KEEP_LEAF", 8));
+  // fast path of the vote: with a handful of BVH nodes (the Cornell boxes: 8) the node class rarely collects 12 waiting lanes and every
+  // iteration would pay the full vote; 8 / 6 there is +27 % on cfg4's renderKernel, 12 / 8 stays the optimum of cfg1-3 (profiles/r2_keep_sweep.log)
+  const bool fewNodes = hs.n_nodes <= 64;
+  a.keepNode = std::max(1u, tuneParam("RTB_KEEP_NODE", fewNodes ? 8 : 12)); a.keepLeaf = std::max(1u, tuneParam("RTB_KEEP_LEAF", fewNodes ? 6 : 8));
   a.lightCap = hs.lightCap;
   a.counter = c->d_counter; a.ctr = instr == 1 ? c->d_counter + kCtrWorkBase : nullptr; a.out = d_out;
   if (plog) { a.plogPrim = plog->prim; a.plogT = plog->t; a.plogStride = plog->stride; }
@@ -594,6 +597,9 @@ int renderLaunch(const HostScene& hs, DeviceCtx* c, const RtRenderParams& q, dou
     a.wfGuideInv = 1.0f / ((float)P * (float)std::max(1u, tuneParam("RTB_WF_GUIDE", 4)));  // a slot asks for 1 / (4 P) of what is left (tools/wf_guide_sweep.py)
     a.wfSort = tuneParam("RTB_WF_SORT", 1);  // block-level material sort of the shade kernel: +4 % once the drain is short (profiles/r2_wf_sort_probe.log; it measured neutral while the drain dominated)
     a.shadeMin = tuneParam("RTB_WF_ITEM_MIN", 8);
+    // the scenes the wavefront is chosen for (<= 64 nodes): 8 / 4 is +4 % over 12 / 8 (profiles/r2_keep_sweep_wavefront.log); a forced wavefront on a
+    // large BVH keeps renderKernel's 12 / 8 (8 / 4 costs cfg1 / cfg2 9 % there)
+    a.keepNode = std::max(1u, tuneParam("RTB_WF_KEEP_NODE", fewNodes ? 8 : 12)); a.keepLeaf = std::max(1u, tuneParam("RTB_WF_KEEP_LEAF", fewNodes ? 4 : 8));
     const unsigned long long lanes = (unsigned long long)c->numSMs * 8ull * kBlock;
     a.chunk = (uint32_t)std::max<unsigned long long>(32, std::min<unsigned long long>(256, P / std::max<unsigned long long>(1, lanes / 32 * 4)));
     const int rounds0 = (int)std::min<unsigned long long>(4096, a.total_paths * tuneParam("RTB_WF_EST_BOUNCES", 4) / P + 24);
@@ -1196,7 +1202,7 @@ int rt_render_device_static(rt_scene_t scene, const RtRenderParams* params, doub
     a.chunk = (uint32_t)chunk;
     a.chunkMin = (uint32_t)std::min<unsigned long long>(chunk, 32);
     a.chunkDiv = (uint32_t)std::max<unsigned long long>(1, warps * 8);
-    a.shadeMin = 16; a.rectMin = hs.n_cuboids > hs.n_rects ? 6u : 3u; a.rareMin = hs.n_media > 0 ? 4u : 8u; a.keepNode = 12; a.keepLeaf = 8;
+    a.shadeMin = 16; a.rectMin = hs.n_cuboids > hs.n_rects ? 6u : 3u; a.rareMin = hs.n_media > 0 ? 4u : 8u; a.keepNode = hs.n_nodes <= 64 ? 8 : 12; a.keepLeaf = hs.n_nodes <= 64 ? 6 : 8;
     a.lightCap = hs.lightCap;
     a.counter = scratch; a.ctr = nullptr; a.out = fb;
     cudaError_t ce;

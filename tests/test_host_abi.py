@@ -222,3 +222,18 @@ def test_traversal_budget_limits_are_reported(R):
     assert rc == -2 and "lights BVH too deep" in msg
     rc, msg = create(**left_chain(3), world_root=BVH | 0, lights_root=BVH | 1)
     assert rc in (0, -3), msg
+
+
+def test_main_example_builds(R, tmp_path):
+    """examples/Main.cpp = app/Main.hs against the C++ mirror: it must compile and link against the two libraries; without a CUDA device it
+    fails loudly (no CPU path), with one it prints the P3 image of the Cornell box."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    pkg_dir = os.path.join(root, "ray-tracing_b200")
+    exe = str(tmp_path / "Main")
+    subprocess.check_call(["g++", "-O1", "-std=c++17", "-I" + os.path.join(pkg_dir, "host"), "-I" + os.path.join(root, "include"), os.path.join(root, "examples", "Main.cpp"),
+                           "-L" + pkg_dir, "-lrt_host", "-lrt_b200", "-Wl,-rpath," + pkg_dir, "-o", exe])
+    if R.core().rt_device_count() > 0:
+        return  # rendering 500x500x1000 belongs to the GPU suite (test_gpu_parity.py renders the same frame through the same mirror)
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 1 and "no CUDA device" in r.stderr and r.stdout == ""
